@@ -1,0 +1,119 @@
+/*
+ * b200sft.h -- C ABI of libb200sft.so: the B200 (sm_100a) data-parallel hot path of the SFT step
+ * of thesteve0/llm-fine-tune-distributed.
+ *
+ * The reference (a Python script, training.py) has no native code; the arithmetic of its step
+ * runs in third-party packages.  Each entry point below names the reference call site it replaces
+ * (paths under the reference checkout) and the third-party function that carries the arithmetic
+ * ("SP/" = site-packages of torch 2.11 / transformers 5.5).
+ *
+ * Conventions
+ *   - every pointer is a CUDA device pointer on the current device unless marked "host";
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - no entry point synchronises the host or allocates device memory: scratch is supplied by the
+ *     caller, sized by the matching *_workspace_bytes() query;
+ *   - return value 0 = success, negative = error (b200sft_last_error() gives the text);
+ *   - bf16 tensors are row-major and 16-byte aligned, with hidden size H and vocabulary V
+ *     multiples of 8 (TMA needs 16-byte row pitches).
+ */
+#ifndef B200SFT_H_
+#define B200SFT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Flags for the fused LM-head + cross-entropy calls. */
+#define B200SFT_FLAG_ROUND_LOGITS_BF16 1u /* round each logit to bf16 before the softmax, as the      \
+                                             reference does between lm_head (bf16 out) and            \
+                                             logits.float() -- SP/transformers/loss/loss_utils.py:55 */
+
+/* How the summed loss is normalised (SP/transformers/loss/loss_utils.py:28-42). */
+#define B200SFT_DENOM_NONE 0   /* loss = scale * sum                                  */
+#define B200SFT_DENOM_DEVICE 1 /* loss = scale * sum / *denom  (num_items_in_batch)    */
+#define B200SFT_DENOM_VALID 2  /* loss = scale * sum / (#rows with label != ignore): the
+                                  reduction="mean" branch taken when num_items_in_batch is None */
+
+const char* b200sft_last_error(void);
+int b200sft_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Label front-end.  Replaces the shift in ForCausalLMLoss (SP/transformers/loss/loss_utils.py:57-60:
+ * pad right with ignore_index, drop the first column, flatten) and the count in
+ * Trainer._get_num_items_in_batch (SP/transformers/trainer.py:2136: labels.ne(-100).sum(), on the
+ * UNSHIFTED labels), both reached from trainer.train() at training.py:300.
+ *   labels   [B,T] int64
+ *   shifted  [B*T] int32  out: shifted[b,t] = labels[b,t+1], last column = ignore_index
+ *   counts   [2]   int64  out: counts[0] = #(labels != ignore) unshifted, counts[1] = same, shifted
+ * Bit-exact integer work.
+ */
+int b200sft_label_prep(const int64_t* labels, int B, int T, int64_t ignore_index, int32_t* shifted,
+                       int64_t* counts, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused LM-head + masked cross-entropy, forward.  Replaces, for training.py:300's step,
+ *   logits = lm_head(hidden)            SP/transformers/models/smollm3/modeling_smollm3.py:504
+ *   logits.float(); cross_entropy(sum)  SP/transformers/loss/loss_utils.py:55,35-36
+ *   loss / num_items_in_batch           SP/transformers/loss/loss_utils.py:37-41
+ * without materialising the [N,V] logits: a TMA-fed tcgen05 GEMM whose epilogue keeps an online
+ * max / sum-exp per row.
+ *   x        [N,H] bf16   final hidden states (already shifted-aligned with `labels`)
+ *   w        [V,H] bf16   lm_head.weight (tied to embed_tokens.weight)
+ *   labels   [N]   int32  shifted labels; ignore_index rows contribute nothing
+ *   denom    int64 scalar (device) used when denom_mode == B200SFT_DENOM_DEVICE, else may be NULL
+ *   loss     fp32 scalar out
+ *   lse      [N] fp32 out: log-sum-exp of every row (saved for backward)
+ *   n_valid  int64 scalar out (may be NULL): #rows with label != ignore_index
+ */
+size_t b200sft_flce_fwd_workspace_bytes(int N, int H, int V);
+int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
+                     int ignore_index, float scale, int denom_mode, const int64_t* denom, uint32_t flags,
+                     float* loss, float* lse, int64_t* n_valid, void* workspace, size_t workspace_bytes,
+                     void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused LM-head + masked cross-entropy, backward.  Replaces autograd's backward of the three
+ * calls above (nll_loss_backward, log_softmax_backward, the fp32->bf16 cast of dlogits and the two
+ * cuBLAS GEMMs dX = dlogits.W, dW = dlogits^T.X).  dlogits = (softmax - onehot) * grad_out * scale
+ * / denom on valid rows, 0 on ignored rows, rounded to bf16 exactly where the reference rounds;
+ * it only ever exists as a [chunk_rows,V] bf16 scratch tile set, never as an [N,V] tensor.
+ *   lse       [N] fp32 from the forward call
+ *   grad_out  fp32 scalar (device): upstream gradient of `loss`
+ *   dx        [N,H] bf16 out
+ *   dw        [V,H] bf16 out (overwritten)
+ *   chunk_rows  rows of dlogits held in scratch at a time (multiple of 128; 0 = library default)
+ */
+size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_rows);
+int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse,
+                     const float* grad_out, int N, int H, int V, int ignore_index, float scale,
+                     int denom_mode, const int64_t* denom, uint32_t flags, int chunk_rows, void* dx, void* dw,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Plain bf16 GEMM on the same tcgen05 engine: C[M,N] = A * B^T, fp32 accumulate, bf16 out.
+ * Exported so the parity tests can pin each operand-layout path of the engine in isolation.
+ *   a_mn_major = 0: A is [M,K] row-major (K contiguous); 1: A is stored [K,M] (M contiguous)
+ *   b_mn_major = 0: B is [N,K] row-major;                1: B is stored [K,N]
+ * lda/ldb/ldc are row pitches in elements.  No reference counterpart (cuBLAS does this there).
+ */
+int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K, int lda, int ldb, int ldc,
+                      int a_mn_major, int b_mn_major, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Gradient-bucket scale / cast kernels for the DDP communication hook.  Replace
+ *   tensor.div_(world_size)                      SP/torch/distributed/algorithms/ddp_comm_hooks/default_hooks.py:18-32
+ *   buffer.to(bf16).div_(world_size); copy back  .../default_hooks.py:57-93 (bf16_compress_hook)
+ * (DDP is configured at training.py:249-256).  128-bit vectorised, grid-stride, HBM-bound.
+ */
+int b200sft_scale_bf16_inplace(void* buf, size_t n, float scale, void* stream);
+int b200sft_scale_f32_inplace(float* buf, size_t n, float scale, void* stream);
+int b200sft_scale_cast_f32_to_bf16(const float* src, void* dst, size_t n, float scale, void* stream);
+int b200sft_cast_bf16_to_f32(const void* src, float* dst, size_t n, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SFT_H_ */

@@ -1,0 +1,258 @@
+// HBM-bound integer / byte kernels of the SFT hot path: the label front-end (shift + counts) and
+// the DDP gradient-bucket scale / cast kernels.  All are grid-stride with 128-bit accesses and a
+// grid sized in multiples of the SM count.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200sft.h"
+#include "capi_common.h"
+
+namespace b200 {
+
+char* last_error_buf() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+
+namespace {
+
+int sm_count() {
+  int dev = 0, n = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n > 0 ? n : 148;
+}
+
+int grid_for(size_t work_items, int threads, int ctas_per_sm) {
+  size_t blocks = (work_items + threads - 1) / threads;
+  size_t cap = static_cast<size_t>(sm_count()) * ctas_per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// label front-end
+// ---------------------------------------------------------------------------------------------
+// shifted[b,t] = labels[b,t+1] (t < T-1), ignore_index at t = T-1; counts of non-ignored entries
+// before and after the shift.  Integer-exact; counts accumulate with 64-bit atomics (order-free).
+__global__ void label_prep_kernel(const int64_t* __restrict__ labels, int B, int T, int64_t ignore_index,
+                                  int32_t* __restrict__ shifted, unsigned long long* __restrict__ counts) {
+  const size_t total = static_cast<size_t>(B) * T;
+  unsigned int c_unshifted = 0, c_shifted = 0;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i % T);
+    const int64_t cur = labels[i];
+    c_unshifted += (cur != ignore_index) ? 1u : 0u;
+    int64_t nxt = ignore_index;
+    if (t + 1 < T) nxt = labels[i + 1];
+    c_shifted += (nxt != ignore_index) ? 1u : 0u;
+    shifted[i] = static_cast<int32_t>(nxt);
+  }
+  // warp -> block -> one atomic pair per block
+  for (int off = 16; off > 0; off >>= 1) {
+    c_unshifted += __shfl_down_sync(0xffffffffu, c_unshifted, off);
+    c_shifted += __shfl_down_sync(0xffffffffu, c_shifted, off);
+  }
+  __shared__ unsigned int s_u[32], s_s[32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_u[warp] = c_unshifted;
+    s_s[warp] = c_shifted;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    unsigned int u = lane < nw ? s_u[lane] : 0u, s = lane < nw ? s_s[lane] : 0u;
+    for (int off = 16; off > 0; off >>= 1) {
+      u += __shfl_down_sync(0xffffffffu, u, off);
+      s += __shfl_down_sync(0xffffffffu, s, off);
+    }
+    if (lane == 0) {
+      atomicAdd(&counts[0], static_cast<unsigned long long>(u));
+      atomicAdd(&counts[1], static_cast<unsigned long long>(s));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// scale / cast (gradient buckets)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t scale_bf16x2(uint32_t v, float s) {
+  __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
+  float2 f = __bfloat1622float2(h);
+  __nv_bfloat162 r = __floats2bfloat162_rn(f.x * s, f.y * s);
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// In place on bf16: 2 B read + 2 B written per element.  Body on 16-byte vectors (8 elements),
+// scalar head/tail for unaligned bucket views.
+__global__ void scale_bf16_kernel(__nv_bfloat16* __restrict__ buf, size_t n, float s) {
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(buf);
+  size_t head = ((16 - (addr & 15)) & 15) / 2;
+  if (head > n) head = n;
+  const size_t nvec = (n - head) / 8;
+  uint4* v = reinterpret_cast<uint4*>(buf + head);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (size_t i = tid; i < nvec; i += stride) {
+    uint4 x = v[i];
+    x.x = scale_bf16x2(x.x, s);
+    x.y = scale_bf16x2(x.y, s);
+    x.z = scale_bf16x2(x.z, s);
+    x.w = scale_bf16x2(x.w, s);
+    v[i] = x;
+  }
+  const size_t tail0 = head + nvec * 8;
+  for (size_t i = tid; i < head + (n - tail0); i += stride) {
+    const size_t j = i < head ? i : tail0 + (i - head);
+    buf[j] = __float2bfloat16_rn(__bfloat162float(buf[j]) * s);
+  }
+}
+
+__global__ void scale_f32_kernel(float* __restrict__ buf, size_t n, float s) {
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(buf);
+  size_t head = ((16 - (addr & 15)) & 15) / 4;
+  if (head > n) head = n;
+  const size_t nvec = (n - head) / 4;
+  float4* v = reinterpret_cast<float4*>(buf + head);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (size_t i = tid; i < nvec; i += stride) {
+    float4 x = v[i];
+    x.x *= s;
+    x.y *= s;
+    x.z *= s;
+    x.w *= s;
+    v[i] = x;
+  }
+  const size_t tail0 = head + nvec * 4;
+  for (size_t i = tid; i < head + (n - tail0); i += stride) {
+    const size_t j = i < head ? i : tail0 + (i - head);
+    buf[j] *= s;
+  }
+}
+
+// fp32 -> bf16 with scale (compress): 4 B read + 2 B written per element.
+__global__ void scale_cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n,
+                                           float s, int vec_ok) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  size_t done = 0;
+  if (vec_ok) {
+    const size_t nvec = n / 8;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    for (size_t i = tid; i < nvec; i += stride) {
+      const float4 a = s4[2 * i], b = s4[2 * i + 1];
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x * s, a.y * s), p1 = __floats2bfloat162_rn(a.z * s, a.w * s);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x * s, b.y * s), p3 = __floats2bfloat162_rn(b.z * s, b.w * s);
+      uint4 o;
+      o.x = *reinterpret_cast<uint32_t*>(&p0);
+      o.y = *reinterpret_cast<uint32_t*>(&p1);
+      o.z = *reinterpret_cast<uint32_t*>(&p2);
+      o.w = *reinterpret_cast<uint32_t*>(&p3);
+      d4[i] = o;
+    }
+    done = nvec * 8;
+  }
+  for (size_t i = done + tid; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i] * s);
+}
+
+// bf16 -> fp32 with scale (decompress): 2 B read + 4 B written per element.
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n, float s,
+                                     int vec_ok) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  size_t done = 0;
+  if (vec_ok) {
+    const size_t nvec = n / 8;
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    for (size_t i = tid; i < nvec; i += stride) {
+      uint4 x = s4[i];
+      const float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&x.x));
+      const float2 b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&x.y));
+      const float2 c = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&x.z));
+      const float2 d = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&x.w));
+      d4[2 * i] = make_float4(a.x * s, a.y * s, b.x * s, b.y * s);
+      d4[2 * i + 1] = make_float4(c.x * s, c.y * s, d.x * s, d.y * s);
+    }
+    done = nvec * 8;
+  }
+  for (size_t i = done + tid; i < n; i += stride) dst[i] = __bfloat162float(src[i]) * s;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+const char* b200sft_last_error(void) { return last_error_buf(); }
+int b200sft_version(void) { return 100; }
+
+int b200sft_label_prep(const int64_t* labels, int B, int T, int64_t ignore_index, int32_t* shifted, int64_t* counts,
+                       void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (B < 0 || T < 0) return fail(B200SFT_ERR_INVALID, "negative label shape %d x %d", B, T);
+  if (!counts) return fail(B200SFT_ERR_INVALID, "null counts pointer");
+  B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), stream));
+  const size_t total = static_cast<size_t>(B) * T;
+  if (total == 0) return B200SFT_OK;  // empty batch: both counts are zero
+  if (!labels || !shifted) return fail(B200SFT_ERR_INVALID, "null label pointer");
+  const int threads = 256;
+  label_prep_kernel<<<grid_for(total, threads, 8), threads, 0, stream>>>(
+      labels, B, T, ignore_index, shifted, reinterpret_cast<unsigned long long*>(counts));
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_scale_bf16_inplace(void* buf, size_t n, float scale, void* stream_) {
+  if (n == 0) return B200SFT_OK;
+  if (!buf) return fail(B200SFT_ERR_INVALID, "null buffer");
+  if (reinterpret_cast<uintptr_t>(buf) & 1) return fail(B200SFT_ERR_INVALID, "bf16 buffer must be 2-byte aligned");
+  const int threads = 256;
+  scale_bf16_kernel<<<grid_for((n + 7) / 8, threads, 8), threads, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<__nv_bfloat16*>(buf), n, scale);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_scale_f32_inplace(float* buf, size_t n, float scale, void* stream_) {
+  if (n == 0) return B200SFT_OK;
+  if (!buf) return fail(B200SFT_ERR_INVALID, "null buffer");
+  if (reinterpret_cast<uintptr_t>(buf) & 3) return fail(B200SFT_ERR_INVALID, "fp32 buffer must be 4-byte aligned");
+  const int threads = 256;
+  scale_f32_kernel<<<grid_for((n + 3) / 4, threads, 8), threads, 0, static_cast<cudaStream_t>(stream_)>>>(buf, n, scale);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_scale_cast_f32_to_bf16(const float* src, void* dst, size_t n, float scale, void* stream_) {
+  if (n == 0) return B200SFT_OK;
+  if (!src || !dst) return fail(B200SFT_ERR_INVALID, "null buffer");
+  const int vec_ok = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) ? 1 : 0;
+  const int threads = 256;
+  scale_cast_f32_bf16_kernel<<<grid_for((n + 7) / 8, threads, 8), threads, 0, static_cast<cudaStream_t>(stream_)>>>(
+      src, static_cast<__nv_bfloat16*>(dst), n, scale, vec_ok);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_cast_bf16_to_f32(const void* src, float* dst, size_t n, float scale, void* stream_) {
+  if (n == 0) return B200SFT_OK;
+  if (!src || !dst) return fail(B200SFT_ERR_INVALID, "null buffer");
+  const int vec_ok = ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) ? 1 : 0;
+  const int threads = 256;
+  cast_bf16_f32_kernel<<<grid_for((n + 7) / 8, threads, 8), threads, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(src), dst, n, scale, vec_ok);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,561 @@
+// Fused LM-head + masked cross-entropy for sm_100a: the epilogues that specialise the tcgen05
+// GEMM engine (gemm_engine.cuh), the small row-wise kernels around them, and the C-ABI entry
+// points declared in include/b200sft.h.
+//
+// Forward:  logits tile = X[128 rows] . W[256 vocab rows]^T accumulates in TMEM; the epilogue
+//           folds it into a per-row (max, sum-exp) partial and picks the target logit.  A row-wise
+//           kernel merges the per-vocab-tile partials into lse[N]; one block sums the loss.
+// Backward: per chunk of rows, the same GEMM is recomputed and its epilogue emits
+//           dlogits = (exp(z - lse) - onehot) * coef as bf16 into scratch; two more engine GEMMs
+//           produce dX = dlogits . W and dW = dlogits^T . X reading W, X and the scratch through
+//           MN-major descriptors (no transposes in HBM).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/b200sft.h"
+#include "capi_common.h"
+#include "gemm_engine.cuh"
+
+namespace b200 {
+
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+// =============================================================================================
+// Epilogues
+// =============================================================================================
+
+// ---- forward: per-row online softmax statistics over one 256-wide vocabulary tile ------------
+struct FwdSoftmaxEpi {
+  struct Params {
+    const int32_t* labels;  // [M]
+    float2* partials;       // [tiles_n][M]  (max, sum exp(z - max))
+    float* tgt_logit;       // [M]
+    int round_bf16;
+  };
+  const Params& p;
+  const int M, N;
+  float run_m, run_s;
+  int lbl, row;
+
+  __device__ FwdSoftmaxEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {}
+
+  __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) {
+    row = tc.m0 + row_in_tile;
+    run_m = -INFINITY;
+    run_s = 0.f;
+    lbl = (row < M) ? __ldg(p.labels + row) : -1;
+  }
+
+  __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
+    const int col0 = tc.n0 + c;
+    if (col0 >= N) return;
+    float z[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) z[j] = __uint_as_float(acc[j]);
+    if (p.round_bf16) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) z[j] = round_to_bf16(z[j]);
+    }
+    if (col0 + 32 > N) {  // ragged last vocabulary tile
+#pragma unroll
+      for (int j = 0; j < 32; ++j) z[j] = (col0 + j < N) ? z[j] : -INFINITY;
+    }
+    float cmax = z[0];
+#pragma unroll
+    for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, z[j]);
+    const float new_m = fmaxf(run_m, cmax);  // finite: at least one real column in this chunk
+    const float nm2 = new_m * LOG2E;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      s0 += ex2_approx(fmaf(z[j + 0], LOG2E, -nm2));
+      s1 += ex2_approx(fmaf(z[j + 1], LOG2E, -nm2));
+      s2 += ex2_approx(fmaf(z[j + 2], LOG2E, -nm2));
+      s3 += ex2_approx(fmaf(z[j + 3], LOG2E, -nm2));
+    }
+    run_s = run_s * ex2_approx((run_m - new_m) * LOG2E) + ((s0 + s1) + (s2 + s3));
+    run_m = new_m;
+    if (lbl >= col0 && lbl < col0 + 32) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) t = (col0 + j == lbl) ? z[j] : t;
+      if (row < M) p.tgt_logit[row] = t;
+    }
+  }
+
+  __device__ __forceinline__ void tile_end(const TileCoord& tc, int) {
+    if (row < M) p.partials[static_cast<size_t>(tc.tile_n) * M + row] = make_float2(run_m, run_s);
+  }
+};
+
+// ---- backward stage 1: dlogits tile -> bf16 scratch --------------------------------------------
+struct DlogitsEpi {
+  struct Params {
+    const int32_t* labels;  // [M] (chunk-local)
+    const float* lse;       // [M]
+    const float* grad_out;  // device scalar
+    const int64_t* denom;   // device scalar or nullptr
+    float scale;
+    int ignore_index;
+    int round_bf16;
+    __nv_bfloat16* out;  // [M][ld]
+    int ld;
+  };
+  const Params& p;
+  const int M, N;
+  float coef_all, coef, lse2;
+  int lbl, row;
+
+  __device__ DlogitsEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {
+    float c = __ldg(p.grad_out) * p.scale;
+    if (p.denom != nullptr) c = c / static_cast<float>(__ldg(p.denom));
+    coef_all = c;
+  }
+
+  __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) {
+    row = tc.m0 + row_in_tile;
+    lbl = p.ignore_index;
+    lse2 = 0.f;
+    if (row < M) {
+      lbl = __ldg(p.labels + row);
+      lse2 = __ldg(p.lse + row) * LOG2E;
+    }
+    coef = (lbl != p.ignore_index) ? coef_all : 0.f;
+  }
+
+  __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
+    const int col0 = tc.n0 + c;
+    if (col0 >= N || row >= M) return;
+    float g[32];
+    if (coef == 0.f && lbl == p.ignore_index) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) g[j] = 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float z = __uint_as_float(acc[j]);
+        if (p.round_bf16) z = round_to_bf16(z);
+        float pr = ex2_approx(fmaf(z, LOG2E, -lse2));
+        pr = (col0 + j == lbl) ? pr - 1.f : pr;
+        g[j] = pr * coef;
+      }
+    }
+    __nv_bfloat16* dst = p.out + static_cast<size_t>(row) * p.ld + col0;
+    if (col0 + 32 <= N) {
+      uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 v;
+        v.x = pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1]);
+        v.y = pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3]);
+        v.z = pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5]);
+        v.w = pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]);
+        d4[q] = v;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < N) dst[j] = __float2bfloat16_rn(g[j]);
+    }
+  }
+
+  __device__ __forceinline__ void tile_end(const TileCoord&, int) {}
+};
+
+// ---- plain store epilogue (dX, dW, exported GEMM) ----------------------------------------------
+enum StoreMode { STORE_BF16 = 0, STORE_F32 = 1, ACCUM_F32 = 2, ACCUM_F32_OUT_BF16 = 3 };
+
+struct StoreEpi {
+  struct Params {
+    __nv_bfloat16* out;  // [M][ld] bf16 (modes 0, 3)
+    float* acc;          // [M][ld] fp32 (modes 1, 2, 3)
+    int ld;
+    int mode;
+  };
+  const Params& p;
+  const int M, N;
+  int row;
+
+  __device__ StoreEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {}
+  __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) { row = tc.m0 + row_in_tile; }
+
+  __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
+    const int col0 = tc.n0 + c;
+    if (col0 >= N || row >= M) return;
+    const size_t off = static_cast<size_t>(row) * p.ld + col0;
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+    const bool full = (col0 + 32 <= N);
+    if (p.mode != STORE_BF16) {
+      float* a = p.acc + off;
+      if (full) {
+        float4* a4 = reinterpret_cast<float4*>(a);
+        if (p.mode != STORE_F32) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            float4 t = a4[q];
+            v[q * 4 + 0] += t.x;
+            v[q * 4 + 1] += t.y;
+            v[q * 4 + 2] += t.z;
+            v[q * 4 + 3] += t.w;
+          }
+        }
+        if (p.mode != ACCUM_F32_OUT_BF16) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) a4[q] = make_float4(v[q * 4 + 0], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (col0 + j < N) {
+            if (p.mode != STORE_F32) v[j] += a[j];
+            if (p.mode != ACCUM_F32_OUT_BF16) a[j] = v[j];
+          }
+        }
+      }
+    }
+    if (p.mode == STORE_BF16 || p.mode == ACCUM_F32_OUT_BF16) {
+      __nv_bfloat16* dst = p.out + off;
+      if (full) {
+        uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 t;
+          t.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
+          t.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+          t.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
+          t.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+          d4[q] = t;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < N) dst[j] = __float2bfloat16_rn(v[j]);
+      }
+    }
+  }
+  __device__ __forceinline__ void tile_end(const TileCoord&, int) {}
+};
+
+// =============================================================================================
+// Row-wise kernels around the forward GEMM
+// =============================================================================================
+
+// Merge the per-vocabulary-tile (max, sumexp) partials of each row into lse, and emit the row's
+// loss term (lse - target logit) or 0 for ignored rows.
+__global__ void flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ tgt_logit,
+                                       const int32_t* __restrict__ labels, int M, int tiles_n, int ignore_index,
+                                       float* __restrict__ lse, float* __restrict__ row_loss) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= M) return;
+  float m = -INFINITY;
+  for (int t = 0; t < tiles_n; ++t) m = fmaxf(m, partials[static_cast<size_t>(t) * M + row].x);
+  float s = 0.f;
+  for (int t = 0; t < tiles_n; ++t) {
+    const float2 pr = partials[static_cast<size_t>(t) * M + row];
+    s += pr.y * exp2f((pr.x - m) * LOG2E);
+  }
+  const float l = m + logf(s);
+  lse[row] = l;
+  const int lbl = labels[row];
+  row_loss[row] = (lbl != ignore_index) ? (l - tgt_logit[row]) : 0.f;
+}
+
+// One block: fixed-order (deterministic) sum of the row losses and count of valid rows.
+__global__ void flce_reduce_loss_kernel(const float* __restrict__ row_loss, const int32_t* __restrict__ labels,
+                                        int M, int ignore_index, float scale, int denom_mode,
+                                        const int64_t* __restrict__ denom, float* __restrict__ loss,
+                                        int64_t* __restrict__ n_valid) {
+  __shared__ double s_sum[1024];
+  __shared__ int s_cnt[1024];
+  double acc = 0.0;
+  int cnt = 0;
+  for (int i = threadIdx.x; i < M; i += blockDim.x) {
+    acc += static_cast<double>(row_loss[i]);
+    cnt += (labels[i] != ignore_index) ? 1 : 0;
+  }
+  s_sum[threadIdx.x] = acc;
+  s_cnt[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int off = blockDim.x >> 1; off > 0; off >>= 1) {
+    if (threadIdx.x < off) {
+      s_sum[threadIdx.x] += s_sum[threadIdx.x + off];
+      s_cnt[threadIdx.x] += s_cnt[threadIdx.x + off];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    float total = static_cast<float>(s_sum[0]) * scale;
+    if (denom_mode == B200SFT_DENOM_DEVICE) total = total / static_cast<float>(*denom);
+    if (denom_mode == B200SFT_DENOM_VALID) total = total / static_cast<float>(s_cnt[0]);  // 0/0 = NaN, as torch
+    *loss = total;
+    if (n_valid != nullptr) *n_valid = static_cast<int64_t>(s_cnt[0]);
+  }
+}
+
+// =============================================================================================
+// Host side
+// =============================================================================================
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 2-D tensor map with 128-byte swizzle.  `inner` elements are contiguous; rows are `ld`
+// elements apart.  Out-of-bounds box elements read as zero (they add nothing to the MMA).
+int make_tmap(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+              uint32_t box_outer) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return fail(B200SFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (ld * 2) % 16 != 0)
+    return fail(B200SFT_ERR_INVALID, "TMA operand needs a 16-byte aligned base and row pitch (ld=%llu)",
+                (unsigned long long)ld);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(B200SFT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return B200SFT_OK;
+}
+
+// Operand map: K-major = [rows][K] with K contiguous; MN-major = [K][rows] with rows contiguous.
+int make_operand_tmap(CUtensorMap* m, const void* base, int rows, int K, int ld, bool mn_major, int block_rows) {
+  if (!mn_major) return make_tmap(m, base, K, rows, ld, BLOCK_K, block_rows);
+  return make_tmap(m, base, rows, K, ld, 64, BLOCK_K);
+}
+
+int num_sms() {
+  static int sms[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (sms[dev] == 0) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+  return sms[dev] > 0 ? sms[dev] : 148;
+}
+
+template <class Epi, bool A_MN, bool B_MN>
+int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
+                const typename Epi::Params& ep, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
+  CUtensorMap ta, tb;
+  int rc = make_operand_tmap(&ta, a, M, K, lda, A_MN, BLOCK_M);
+  if (rc != 0) return rc;
+  rc = make_operand_tmap(&tb, b, N, K, ldb, B_MN, BLOCK_N);
+  if (rc != 0) return rc;
+  GemmShape s;
+  s.M = M;
+  s.N = N;
+  s.K = K;
+  s.tiles_m = (M + BLOCK_M - 1) / BLOCK_M;
+  s.tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
+  s.m_fastest = m_fastest;
+  auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+  const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
+  const int grid = static_cast<int>(tiles < num_sms() ? tiles : num_sms());
+  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(ta, tb, s, ep);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+constexpr int DEFAULT_CHUNK_ROWS = 4096;
+
+int resolve_chunk_rows(int N, int chunk_rows) {
+  int c = chunk_rows > 0 ? chunk_rows : DEFAULT_CHUNK_ROWS;
+  c = (c + BLOCK_M - 1) / BLOCK_M * BLOCK_M;
+  const int n_up = (N + BLOCK_M - 1) / BLOCK_M * BLOCK_M;
+  return c < n_up ? c : n_up;
+}
+
+int check_dims(int N, int H, int V) {
+  if (N <= 0 || H <= 0 || V <= 0) return fail(B200SFT_ERR_INVALID, "N, H, V must be positive (got %d, %d, %d)", N, H, V);
+  if (H % 8 != 0 || V % 8 != 0)
+    return fail(B200SFT_ERR_INVALID, "H and V must be multiples of 8 for 16-byte TMA row pitches (got H=%d V=%d)", H, V);
+  return B200SFT_OK;
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+size_t b200sft_flce_fwd_workspace_bytes(int N, int H, int V) {
+  (void)H;
+  if (N <= 0 || V <= 0) return 0;
+  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
+  size_t b = align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);  // partials
+  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // target logits
+  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // row losses
+  return b;
+}
+
+int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N, int H, int V, int ignore_index,
+                     float scale, int denom_mode, const int64_t* denom, uint32_t flags, float* loss, float* lse,
+                     int64_t* n_valid, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int rc = check_dims(N, H, V);
+  if (rc != 0) return rc;
+  if (!x || !w || !labels || !loss || !lse) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (denom_mode == B200SFT_DENOM_DEVICE && denom == nullptr)
+    return fail(B200SFT_ERR_INVALID, "denom_mode DEVICE needs a denom pointer");
+  if (denom_mode < 0 || denom_mode > 2) return fail(B200SFT_ERR_INVALID, "bad denom_mode %d", denom_mode);
+  const size_t need = b200sft_flce_fwd_workspace_bytes(N, H, V);
+  if (workspace == nullptr || workspace_bytes < need)
+    return fail(B200SFT_ERR_WORKSPACE, "flce_fwd workspace too small: have %zu, need %zu", workspace_bytes, need);
+
+  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  float2* partials = reinterpret_cast<float2*>(ws);
+  ws += align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);
+  float* tgt = reinterpret_cast<float*>(ws);
+  ws += align_up(static_cast<size_t>(N) * sizeof(float), 256);
+  float* row_loss = reinterpret_cast<float*>(ws);
+
+  // Rows whose label is ignored (or, defensively, outside [0,V)) never get a target logit written.
+  B200_CUDA_CHECK(cudaMemsetAsync(tgt, 0, static_cast<size_t>(N) * sizeof(float), stream));
+
+  FwdSoftmaxEpi::Params ep;
+  ep.labels = labels;
+  ep.partials = partials;
+  ep.tgt_logit = tgt;
+  ep.round_bf16 = (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0;
+  rc = launch_gemm<FwdSoftmaxEpi, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream);
+  if (rc != 0) return rc;
+
+  flce_merge_rows_kernel<<<(N + 255) / 256, 256, 0, stream>>>(partials, tgt, labels, N, static_cast<int>(tiles_n),
+                                                               ignore_index, lse, row_loss);
+  B200_CUDA_CHECK(cudaGetLastError());
+  flce_reduce_loss_kernel<<<1, 1024, 0, stream>>>(row_loss, labels, N, ignore_index, scale, denom_mode, denom, loss,
+                                                  n_valid);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_rows) {
+  if (N <= 0 || H <= 0 || V <= 0) return 0;
+  const int c = resolve_chunk_rows(N, chunk_rows);
+  size_t b = align_up(static_cast<size_t>(c) * V * sizeof(__nv_bfloat16), 1024);  // dlogits chunk
+  if (c < N) b += align_up(static_cast<size_t>(V) * H * sizeof(float), 1024);     // fp32 dW accumulator
+  return b;
+}
+
+int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse, const float* grad_out,
+                     int N, int H, int V, int ignore_index, float scale, int denom_mode, const int64_t* denom,
+                     uint32_t flags, int chunk_rows, void* dx, void* dw, void* workspace, size_t workspace_bytes,
+                     void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int rc = check_dims(N, H, V);
+  if (rc != 0) return rc;
+  if (!x || !w || !labels || !lse || !grad_out || !dx || !dw) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (denom_mode == B200SFT_DENOM_VALID)
+    return fail(B200SFT_ERR_INVALID,
+                "backward takes the valid-row count as a device scalar: pass n_valid from the forward call with "
+                "denom_mode DEVICE");
+  if (denom_mode == B200SFT_DENOM_DEVICE && denom == nullptr)
+    return fail(B200SFT_ERR_INVALID, "denom_mode DEVICE needs a denom pointer");
+  const size_t need = b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_rows);
+  if (workspace == nullptr || workspace_bytes < need)
+    return fail(B200SFT_ERR_WORKSPACE, "flce_bwd workspace too small: have %zu, need %zu", workspace_bytes, need);
+
+  const int chunk = resolve_chunk_rows(N, chunk_rows);
+  const int num_chunks = (N + chunk - 1) / chunk;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  __nv_bfloat16* dlog = reinterpret_cast<__nv_bfloat16*>(ws);
+  ws += align_up(static_cast<size_t>(chunk) * V * sizeof(__nv_bfloat16), 1024);
+  float* dw_acc = (num_chunks > 1) ? reinterpret_cast<float*>(ws) : nullptr;
+
+  const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+
+  for (int ci = 0; ci < num_chunks; ++ci) {
+    const int r0 = ci * chunk;
+    const int rows = (N - r0) < chunk ? (N - r0) : chunk;
+    const __nv_bfloat16* xc = xb + static_cast<size_t>(r0) * H;
+
+    // (1) dlogits[rows,V] = (softmax(Xc.W^T) - onehot) * coef   (recompute, epilogue-fused)
+    DlogitsEpi::Params dp;
+    dp.labels = labels + r0;
+    dp.lse = lse + r0;
+    dp.grad_out = grad_out;
+    dp.denom = (denom_mode == B200SFT_DENOM_DEVICE) ? denom : nullptr;
+    dp.scale = scale;
+    dp.ignore_index = ignore_index;
+    dp.round_bf16 = (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0;
+    dp.out = dlog;
+    dp.ld = V;
+    rc = launch_gemm<DlogitsEpi, false, false>(xc, H, w, H, rows, V, H, /*m_fastest=*/1, dp, stream);
+    if (rc != 0) return rc;
+
+    // (2) dX[rows,H] = dlogits[rows,V] . W[V,H]      A K-major (V contiguous), B = W read MN-major
+    StoreEpi::Params sx;
+    sx.out = dxb + static_cast<size_t>(r0) * H;
+    sx.acc = nullptr;
+    sx.ld = H;
+    sx.mode = STORE_BF16;
+    rc = launch_gemm<StoreEpi, false, true>(dlog, V, w, H, rows, H, V, /*m_fastest=*/0, sx, stream);
+    if (rc != 0) return rc;
+
+    // (3) dW[V,H] (+)= dlogits^T[V,rows] . Xc[rows,H]   both operands read MN-major
+    StoreEpi::Params sw;
+    sw.out = static_cast<__nv_bfloat16*>(dw);
+    sw.acc = dw_acc;
+    sw.ld = H;
+    if (num_chunks == 1)
+      sw.mode = STORE_BF16;
+    else if (ci == 0)
+      sw.mode = STORE_F32;
+    else if (ci == num_chunks - 1)
+      sw.mode = ACCUM_F32_OUT_BF16;
+    else
+      sw.mode = ACCUM_F32;
+    rc = launch_gemm<StoreEpi, true, true>(dlog, V, xc, H, V, H, rows, /*m_fastest=*/0, sw, stream);
+    if (rc != 0) return rc;
+  }
+  return B200SFT_OK;
+}
+
+int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K, int lda, int ldb, int ldc,
+                      int a_mn_major, int b_mn_major, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!a || !b || !c) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (ldc % 8 != 0) return fail(B200SFT_ERR_INVALID, "ldc must be a multiple of 8");
+  StoreEpi::Params sp;
+  sp.out = static_cast<__nv_bfloat16*>(c);
+  sp.acc = nullptr;
+  sp.ld = ldc;
+  sp.mode = STORE_BF16;
+  if (!a_mn_major && !b_mn_major) return launch_gemm<StoreEpi, false, false>(a, lda, b, ldb, M, N, K, 0, sp, stream);
+  if (!a_mn_major && b_mn_major) return launch_gemm<StoreEpi, false, true>(a, lda, b, ldb, M, N, K, 0, sp, stream);
+  if (a_mn_major && !b_mn_major) return launch_gemm<StoreEpi, true, false>(a, lda, b, ldb, M, N, K, 0, sp, stream);
+  return launch_gemm<StoreEpi, true, true>(a, lda, b, ldb, M, N, K, 0, sp, stream);
+}
+
+}  // extern "C"

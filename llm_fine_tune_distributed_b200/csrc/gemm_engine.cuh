@@ -1,0 +1,217 @@
+// Persistent, warp-specialised tcgen05 GEMM engine for sm_100a.
+//
+//   D[M,N] (fp32, TMEM) = A[M,K] (bf16) * B[N,K]^T (bf16)
+//
+// One CTA per SM loops over 128x256 output tiles.  Warp 0 streams A/B k-blocks into a 4-deep
+// shared-memory ring with TMA (128-byte swizzle), warp 1 issues tcgen05.mma from one thread into
+// one of two 256-column TMEM accumulator stages, warps 2..5 drain the other stage with tcgen05.ld
+// and run the fused epilogue, so the epilogue of tile i overlaps the MMAs of tile i+1.  The
+// epilogue is a functor; the LM-head/cross-entropy kernels differ only there (flce.cu).
+//
+// Either operand may be K-major (K contiguous in global memory) or MN-major (M or N contiguous):
+// the data-gradient GEMMs read the same row-major tensors transposed, and MN-major descriptors
+// avoid materialising transposes in HBM.
+#pragma once
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_N = 256;
+constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_STAGES = 4;
+constexpr int NUM_ACC_STAGES = 2;
+constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KiB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int TMEM_COLS = NUM_ACC_STAGES * BLOCK_N;  // 512: the whole TMEM of the SM
+constexpr int NUM_EPI_WARPS = 4;
+constexpr int GEMM_THREADS = 32 * (2 + NUM_EPI_WARPS);
+constexpr int SMEM_BARRIER_BYTES = 256;
+constexpr int GEMM_SMEM_BYTES = NUM_STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + SMEM_BARRIER_BYTES;
+
+struct GemmShape {
+  int M, N, K;
+  int tiles_m, tiles_n;
+  int m_fastest;  // tile order: 1 = consecutive CTAs walk M for a fixed N tile (shares the B panel in L2)
+};
+
+struct TileCoord {
+  int m0, n0, tile_m, tile_n;
+};
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
+  TileCoord c;
+  if (s.m_fastest) {
+    c.tile_m = tile % s.tiles_m;
+    c.tile_n = tile / s.tiles_m;
+  } else {
+    c.tile_n = tile % s.tiles_n;
+    c.tile_m = tile / s.tiles_n;
+  }
+  c.m0 = c.tile_m * BLOCK_M;
+  c.n0 = c.tile_n * BLOCK_N;
+  return c;
+}
+
+// Epilogue contract:
+//   struct Epi { struct Params {...};
+//     __device__ Epi(const Params&, const GemmShape&);
+//     // called by each of the 128 epilogue threads; `row_in_tile` = TMEM lane owned by the thread
+//     __device__ void tile_begin(const TileCoord&, int row_in_tile);
+//     __device__ void chunk(const TileCoord&, int row_in_tile, int col_in_tile /*0,32,..*/, const uint32_t (&acc)[32]);
+//     __device__ void tile_end(const TileCoord&, int row_in_tile);
+//   };
+template <class Epi, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                        const GemmShape shape, const typename Epi::Params epi_params) {
+  extern __shared__ uint8_t smem_raw[];
+  // 128B-swizzled tiles must be 1024-byte aligned (descriptor base_offset = 0).
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + NUM_STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES);
+  uint64_t* full_bar = bars;                                    // [NUM_STAGES]  TMA -> MMA
+  uint64_t* empty_bar = bars + NUM_STAGES;                      // [NUM_STAGES]  MMA -> TMA
+  uint64_t* acc_full_bar = bars + 2 * NUM_STAGES;               // [2] MMA -> epilogue
+  uint64_t* acc_empty_bar = bars + 2 * NUM_STAGES + NUM_ACC_STAGES;  // [2] epilogue -> MMA
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * NUM_STAGES + 2 * NUM_ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = shape.tiles_m * shape.tiles_n;
+  const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int i = 0; i < NUM_STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < NUM_ACC_STAGES; ++i) {
+      mbar_init(&acc_full_bar[i], 1);
+      mbar_init(&acc_empty_bar[i], NUM_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_ptr_smem, TMEM_COLS);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ------------------------------- TMA producer -------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(shape, tile);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+          uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+          uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+          const int k0 = kb * BLOCK_K;
+          if constexpr (!A_MN) {
+            tma_load_2d(&tmap_a, &full_bar[stage], sa, k0, tc.m0);  // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / 64; ++j)  // box {64 m, 64 k-rows} per 64-wide M block
+              tma_load_2d(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(&tmap_b, &full_bar[stage], sb, k0, tc.n0);  // box {64 k, 256 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), tc.n0 + j * 64, k0);
+          }
+          if (++stage == NUM_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------- MMA issuer -------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      // K-major, 128B swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO); LBO is ignored (16 B, as CuTe encodes it).
+      // MN-major, 128B swizzle: each 64-wide MN block is [BLOCK_K rows][128 B]; 8 k-rows per
+      // 1024 B group (SBO), next MN block BLOCK_K*128 B further (LBO).
+      constexpr uint32_t A_LBO = A_MN ? BLOCK_K * 128 : 16, B_LBO = B_MN ? BLOCK_K * 128 : 16;
+      constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&acc_empty_bar[as], aphase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(smem_a + stage * A_STAGE_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+            const uint64_t da = make_smem_desc_sw128(a_addr + kk * A_KSTEP, A_LBO, 1024);
+            const uint64_t db = make_smem_desc_sw128(b_addr + kk * B_KSTEP, B_LBO, 1024);
+            umma_bf16<1>(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit<1>(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == NUM_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit<1>(&acc_full_bar[as]);  // accumulator complete -> epilogue
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------- epilogue warps -------------------------------
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int row_in_tile = quarter * 32 + lane;
+    Epi epi(epi_params, shape);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const TileCoord tc = tile_coord(shape, tile);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      epi.tile_begin(tc, row_in_tile);
+      mbar_wait(&acc_full_bar[as], aphase);
+      tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t acc[32];
+        __syncwarp();  // epilogue functors may diverge per row; tcgen05.ld is warp-collective
+        tmem_ld_32x32b_x32(taddr + c, acc);
+        tmem_ld_wait();
+        epi.chunk(tc, row_in_tile, c, acc);
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty_bar[as]);
+      epi.tile_end(tc, row_in_tile);
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace b200

@@ -1,0 +1,268 @@
+"""Torch-facing operators over the C ABI (include/b200sft.h).
+
+Each function checks shapes/dtypes, takes device memory and the current stream from torch, and
+calls libb200sft.so through ctypes with raw pointers.  They are registered as torch custom ops
+(namespace ``b200sft``) so they compose with autograd and show up by name in profiler traces.
+
+There is no fallback: CPU tensors are rejected and a missing library raises.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi
+from ._cabi import DENOM_DEVICE, DENOM_NONE, DENOM_VALID, FLAG_ROUND_LOGITS_BF16, check
+
+IGNORE_INDEX = -100  # torch.nn.functional.cross_entropy default, SP/transformers/loss/loss_utils.py:28
+
+__all__ = [
+    "label_prep", "flce_forward", "flce_backward", "gemm_bf16", "scale_", "scale_cast_f32_to_bf16",
+    "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX", "FLAG_ROUND_LOGITS_BF16",
+]
+
+
+def _stream_ptr(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise _cabi.B200SftError("b200sft operators run on CUDA tensors only; there is no CPU fallback")
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# --------------------------------------------------------------------------------------------
+# label front-end
+# --------------------------------------------------------------------------------------------
+def label_prep(labels: torch.Tensor, ignore_index: int = IGNORE_INDEX) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Shift labels left by one and count valid tokens, on the device.
+
+    Mirrors ``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:57-60) and
+    ``Trainer._get_num_items_in_batch`` (SP/transformers/trainer.py:2136).
+    Returns ``(shifted int32 [B*T], counts int64 [2] = (unshifted valid, shifted valid))``.
+    """
+    _require_cuda(labels)
+    if labels.dtype != torch.int64 or labels.dim() != 2:
+        raise ValueError("labels must be an int64 [B, T] tensor")
+    labels = labels.contiguous()
+    B, T = labels.shape
+    with torch.cuda.device(labels.device):
+        shifted = torch.empty(B * T, dtype=torch.int32, device=labels.device)
+        counts = torch.empty(2, dtype=torch.int64, device=labels.device)
+        lib = _cabi.load()
+        check(lib.b200sft_label_prep(_ptr(labels), B, T, ignore_index, _ptr(shifted), _ptr(counts),
+                                     _stream_ptr(labels)), "b200sft_label_prep")
+    return shifted, counts
+
+
+# --------------------------------------------------------------------------------------------
+# fused LM-head + cross-entropy
+# --------------------------------------------------------------------------------------------
+def _check_flce_inputs(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> Tuple[int, int, int]:
+    _require_cuda(x, w, labels)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+        raise ValueError("x and w must be bfloat16")
+    if labels.dtype != torch.int32:
+        raise ValueError("labels must be int32 (use label_prep)")
+    if x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1]:
+        raise ValueError(f"x [N,H] / w [V,H] shape mismatch: {tuple(x.shape)} vs {tuple(w.shape)}")
+    if labels.dim() != 1 or labels.shape[0] != x.shape[0]:
+        raise ValueError("labels must be [N]")
+    if not (x.is_contiguous() and w.is_contiguous() and labels.is_contiguous()):
+        raise ValueError("x, w and labels must be contiguous")
+    return x.shape[0], x.shape[1], w.shape[0]
+
+
+def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: float = 1.0,
+                 denom: Optional[torch.Tensor] = None, reduction_mean: bool = False,
+                 ignore_index: int = IGNORE_INDEX, flags: int = 0
+                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """loss, lse, n_valid = fused lm_head + cross-entropy forward; no [N,V] tensor is allocated.
+
+    ``loss = scale * sum_valid(lse - z_target) / D`` with D = 1, ``*denom`` (int64 device scalar,
+    the trainer's num_items_in_batch) or the local valid-row count (``reduction_mean``).
+    """
+    N, H, V = _check_flce_inputs(x, w, labels)
+    if denom is not None and reduction_mean:
+        raise ValueError("pass either denom or reduction_mean")
+    if denom is not None:
+        _require_cuda(denom)
+        if denom.dtype != torch.int64 or denom.numel() != 1:
+            raise ValueError("denom must be a single int64 on the device")
+    mode = DENOM_DEVICE if denom is not None else (DENOM_VALID if reduction_mean else DENOM_NONE)
+    lib = _cabi.load()
+    with torch.cuda.device(x.device):
+        ws_bytes = lib.b200sft_flce_fwd_workspace_bytes(N, H, V)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+        loss = torch.empty((), dtype=torch.float32, device=x.device)
+        lse = torch.empty(N, dtype=torch.float32, device=x.device)
+        n_valid = torch.empty((), dtype=torch.int64, device=x.device)
+        check(lib.b200sft_flce_fwd(_ptr(x), _ptr(w), _ptr(labels), N, H, V, ignore_index, float(scale), mode,
+                                   _ptr(denom), flags, _ptr(loss), _ptr(lse), _ptr(n_valid), _ptr(ws), ws_bytes,
+                                   _stream_ptr(x)), "b200sft_flce_fwd")
+    return loss, lse, n_valid
+
+
+def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
+                  grad_out: torch.Tensor, scale: float = 1.0, denom: Optional[torch.Tensor] = None,
+                  ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_rows: int = 0
+                  ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """dx [N,H] bf16, dw [V,H] bf16 for the loss produced by :func:`flce_forward`."""
+    N, H, V = _check_flce_inputs(x, w, labels)
+    _require_cuda(lse, grad_out)
+    if lse.dtype != torch.float32 or lse.shape != (N,):
+        raise ValueError("lse must be float32 [N]")
+    grad_out = grad_out.to(torch.float32).reshape(()).contiguous()
+    mode = DENOM_DEVICE if denom is not None else DENOM_NONE
+    lib = _cabi.load()
+    with torch.cuda.device(x.device):
+        ws_bytes = lib.b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_rows)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+        dx = torch.empty_like(x)
+        dw = torch.empty_like(w)
+        check(lib.b200sft_flce_bwd(_ptr(x), _ptr(w), _ptr(labels), _ptr(lse), _ptr(grad_out), N, H, V,
+                                   ignore_index, float(scale), mode, _ptr(denom), flags, chunk_rows, _ptr(dx),
+                                   _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
+    return dx, dw
+
+
+def gemm_bf16(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, a_mn_major: bool = False,
+              b_mn_major: bool = False) -> torch.Tensor:
+    """C[M,N] = A . B^T on the tcgen05 engine.  A is [M,K] (or [K,M] when ``a_mn_major``), B is
+    [N,K] (or [K,N] when ``b_mn_major``).  Test hook for the engine's operand layouts."""
+    _require_cuda(a, b)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or not a.is_contiguous() or not b.is_contiguous():
+        raise ValueError("a and b must be contiguous bfloat16")
+    exp_a = (K, M) if a_mn_major else (M, K)
+    exp_b = (K, N) if b_mn_major else (N, K)
+    if tuple(a.shape) != exp_a or tuple(b.shape) != exp_b:
+        raise ValueError(f"expected a {exp_a}, b {exp_b}; got {tuple(a.shape)}, {tuple(b.shape)}")
+    ldc = (N + 7) // 8 * 8
+    lib = _cabi.load()
+    with torch.cuda.device(a.device):
+        c = torch.empty(M, ldc, dtype=torch.bfloat16, device=a.device)
+        check(lib.b200sft_gemm_bf16(_ptr(a), _ptr(b), _ptr(c), M, N, K, a.shape[1], b.shape[1], ldc,
+                                    int(a_mn_major), int(b_mn_major), _stream_ptr(a)), "b200sft_gemm_bf16")
+    return c[:, :N]
+
+
+# --------------------------------------------------------------------------------------------
+# gradient-bucket scale / cast
+# --------------------------------------------------------------------------------------------
+def scale_(buf: torch.Tensor, scale: float) -> torch.Tensor:
+    """In-place ``buf *= scale`` for a contiguous bf16 or fp32 bucket (default_hooks.py:18-32's div_)."""
+    _require_cuda(buf)
+    if not buf.is_contiguous():
+        raise ValueError("bucket must be contiguous")
+    lib = _cabi.load()
+    with torch.cuda.device(buf.device):
+        if buf.dtype == torch.bfloat16:
+            check(lib.b200sft_scale_bf16_inplace(_ptr(buf), buf.numel(), float(scale), _stream_ptr(buf)),
+                  "b200sft_scale_bf16_inplace")
+        elif buf.dtype == torch.float32:
+            check(lib.b200sft_scale_f32_inplace(_ptr(buf), buf.numel(), float(scale), _stream_ptr(buf)),
+                  "b200sft_scale_f32_inplace")
+        else:
+            raise ValueError(f"unsupported bucket dtype {buf.dtype}")
+    return buf
+
+
+def scale_cast_f32_to_bf16(src: torch.Tensor, scale: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bf16(src * scale): the compress half of bf16_compress_hook (default_hooks.py:57-93)."""
+    _require_cuda(src)
+    if src.dtype != torch.float32 or not src.is_contiguous():
+        raise ValueError("src must be contiguous float32")
+    lib = _cabi.load()
+    with torch.cuda.device(src.device):
+        if out is None:
+            out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+        check(lib.b200sft_scale_cast_f32_to_bf16(_ptr(src), _ptr(out), src.numel(), float(scale), _stream_ptr(src)),
+              "b200sft_scale_cast_f32_to_bf16")
+    return out
+
+
+def cast_bf16_to_f32(src: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+    """out = fp32(src) * scale: the decompress half of bf16_compress_hook."""
+    _require_cuda(src, out)
+    if src.dtype != torch.bfloat16 or out.dtype != torch.float32 or src.numel() != out.numel():
+        raise ValueError("src bf16 / out fp32 of equal size expected")
+    lib = _cabi.load()
+    with torch.cuda.device(src.device):
+        check(lib.b200sft_cast_bf16_to_f32(_ptr(src), _ptr(out), src.numel(), float(scale), _stream_ptr(src)),
+              "b200sft_cast_bf16_to_f32")
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# torch custom ops + autograd
+# --------------------------------------------------------------------------------------------
+@torch.library.custom_op("b200sft::flce_fwd", mutates_args=())
+def _flce_fwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: float,
+                 denom: Optional[torch.Tensor], reduction_mean: bool, ignore_index: int,
+                 flags: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    return flce_forward(x, w, labels, scale, denom, reduction_mean, ignore_index, flags)
+
+
+@_flce_fwd_op.register_fake
+def _(x, w, labels, scale, denom, reduction_mean, ignore_index, flags):
+    return (x.new_empty((), dtype=torch.float32), x.new_empty((x.shape[0],), dtype=torch.float32),
+            x.new_empty((), dtype=torch.int64))
+
+
+@torch.library.custom_op("b200sft::flce_bwd", mutates_args=())
+def _flce_bwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
+                 grad_out: torch.Tensor, scale: float, denom: Optional[torch.Tensor], ignore_index: int,
+                 flags: int, chunk_rows: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_rows)
+
+
+@_flce_bwd_op.register_fake
+def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_rows):
+    return torch.empty_like(x), torch.empty_like(w)
+
+
+class _FusedLinearCrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_rows):
+        loss, lse, n_valid = torch.ops.b200sft.flce_fwd(x, w, labels, scale, denom, reduction_mean, ignore_index,
+                                                        flags)
+        # reduction="mean" divides by the local valid count; backward takes it as a device scalar
+        bwd_denom = n_valid if reduction_mean else denom
+        ctx.save_for_backward(x, w, labels, lse, bwd_denom)
+        ctx.scale, ctx.ignore_index, ctx.flags, ctx.chunk_rows = scale, ignore_index, flags, chunk_rows
+        ctx.mark_non_differentiable(lse, n_valid)
+        return loss, lse, n_valid
+
+    @staticmethod
+    def backward(ctx, grad_loss, _g_lse, _g_nvalid):
+        x, w, labels, lse, bwd_denom = ctx.saved_tensors
+        dx, dw = torch.ops.b200sft.flce_bwd(x, w, labels, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
+                                            ctx.flags, ctx.chunk_rows)
+        return dx, dw, None, None, None, None, None, None, None
+
+
+def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,
+                               num_items_in_batch: Optional[torch.Tensor] = None, scale: float = 1.0,
+                               ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_rows: int = 0
+                               ) -> torch.Tensor:
+    """Differentiable ``cross_entropy(hidden @ weight.T, shifted_labels)`` without the logits.
+
+    ``num_items_in_batch`` None -> mean over local valid rows (``reduction="mean"``), else the
+    sum divided by that device scalar -- SP/transformers/loss/loss_utils.py:28-42.
+    ``hidden`` is [N,H] bf16, ``weight`` [V,H] bf16, ``shifted_labels`` int32 [N] from
+    :func:`label_prep`.
+    """
+    denom = None
+    if num_items_in_batch is not None:
+        if not torch.is_tensor(num_items_in_batch):
+            num_items_in_batch = torch.tensor(int(num_items_in_batch), dtype=torch.int64, device=hidden.device)
+        denom = num_items_in_batch.to(device=hidden.device, dtype=torch.int64).reshape(())
+    loss, _, _ = _FusedLinearCrossEntropy.apply(hidden, weight, shifted_labels, float(scale), denom,
+                                                num_items_in_batch is None, ignore_index, flags, chunk_rows)
+    return loss

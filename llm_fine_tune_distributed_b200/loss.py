@@ -1,0 +1,191 @@
+"""Seam #1: the ``Trainer.compute_loss`` override that routes the LM head + cross-entropy of a HF
+causal-LM through the fused sm_100a kernels.
+
+The reference trains with ``trl.SFTTrainer`` (training.py:289-300); its loss is produced inside
+``SmolLM3ForCausalLM.forward`` (SP/transformers/models/smollm3/modeling_smollm3.py:501-508):
+``logits = self.lm_head(hidden)`` then ``self.loss_function(logits, labels, vocab_size, **kwargs)``.
+Both calls are attribute look-ups on the model, so the drop-in is done without touching
+transformers:
+
+* ``model.lm_head`` becomes a :class:`FusedLMHead` that owns the *same* weight Parameter under the
+  same name (state-dict key ``lm_head.weight`` and the tie to ``embed_tokens.weight`` are
+  unchanged) and, while the fused path is armed, returns the hidden states untouched;
+* ``model.loss_function`` becomes :func:`fused_causal_lm_loss`, which receives those hidden states
+  in place of logits and calls the fused forward/backward.
+
+The model is still invoked as ``model(**inputs)`` -- through ``DistributedDataParallel.forward``
+when wrapped -- so DDP's reducer is armed exactly as in the reference.  Outside the armed context
+(``generate``, plain ``model(input_ids)``) the head is an ordinary linear layer.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Any, Optional, Tuple, Union
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+__all__ = ["FusedLMHead", "install_fused_head", "fused_head_armed", "fused_causal_lm_loss", "FusedCELossMixin"]
+
+
+class FusedLMHead(nn.Module):
+    """Stand-in for ``nn.Linear(hidden, vocab, bias=False)`` that can be bypassed.
+
+    ``weight`` is the original Parameter object, so optimizer state, ``tie_weights`` and
+    ``save_pretrained`` see no difference.
+    """
+
+    def __init__(self, linear: nn.Linear):
+        super().__init__()
+        if linear.bias is not None:
+            raise ValueError("the fused head supports bias-free lm_head only (SmolLM3: modeling_smollm3.py:455)")
+        self.in_features = linear.in_features
+        self.out_features = linear.out_features
+        self.weight = linear.weight
+        self.armed = False
+
+    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
+        if self.armed:
+            return hidden_states  # consumed by fused_causal_lm_loss; no [B,T,V] tensor is created
+        return F.linear(hidden_states, self.weight)
+
+    def extra_repr(self) -> str:
+        return f"in_features={self.in_features}, out_features={self.out_features}, bias=False, fused=True"
+
+
+def _unwrap(model: nn.Module) -> nn.Module:
+    while hasattr(model, "module") and isinstance(getattr(model, "module"), nn.Module):
+        model = model.module
+    return model
+
+
+def install_fused_head(model: nn.Module, flags: int = 0, chunk_rows: int = 0) -> nn.Module:
+    """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model."""
+    inner = _unwrap(model)
+    head = getattr(inner, "lm_head", None)
+    if head is None:
+        raise ValueError("model has no lm_head")
+    if not isinstance(head, FusedLMHead):
+        head = FusedLMHead(head)
+        inner.lm_head = head
+    stock_loss = inner.loss_function
+
+    def loss_function(logits, labels, vocab_size=None, **kwargs):
+        if head.armed:
+            return fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_rows=chunk_rows, **kwargs)
+        return stock_loss(logits=logits, labels=labels, vocab_size=vocab_size, **kwargs)
+
+    if not getattr(inner, "_b200sft_patched", False):
+        inner.loss_function = loss_function
+        inner._b200sft_patched = True
+    return inner
+
+
+@contextlib.contextmanager
+def fused_head_armed(model: nn.Module):
+    """While active, ``model(**inputs, labels=...)`` computes its loss with the fused kernels."""
+    head = _unwrap(model).lm_head
+    if not isinstance(head, FusedLMHead):
+        raise RuntimeError("call install_fused_head(model) first")
+    prev = head.armed
+    head.armed = True
+    try:
+        yield
+    finally:
+        head.armed = prev
+
+
+def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                         num_items_in_batch: Optional[Union[torch.Tensor, int]] = None,
+                         ignore_index: int = -100, shift_labels: Optional[torch.Tensor] = None,
+                         flags: int = 0, chunk_rows: int = 0, **_unused: Any) -> torch.Tensor:
+    """``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:45-67) on hidden states.
+
+    Same arguments and meaning, except that the first argument holds ``[B,T,H]`` hidden states:
+    labels are shifted left (or ``shift_labels`` used as given), flattened, and the loss is the
+    sum over non-ignored positions divided by ``num_items_in_batch`` -- or the mean over local
+    non-ignored positions when that is None.
+    """
+    if hidden_states.dim() == 2:
+        hidden_states = hidden_states.unsqueeze(0)
+    B, T, H = hidden_states.shape
+    if shift_labels is None:
+        shifted, _counts = ops.label_prep(labels.to(hidden_states.device).reshape(B, T), ignore_index)
+    else:
+        shifted = shift_labels.to(hidden_states.device).reshape(-1).to(torch.int32).contiguous()
+    h2 = hidden_states.reshape(B * T, H)
+    if h2.dtype != torch.bfloat16:
+        h2 = h2.to(torch.bfloat16)
+    w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
+    return ops.fused_linear_cross_entropy(h2.contiguous(), w.contiguous(), shifted, num_items_in_batch,
+                                          ignore_index=ignore_index, flags=flags, chunk_rows=chunk_rows)
+
+
+class FusedCELossMixin:
+    """Mix into a ``transformers.Trainer`` / ``trl.SFTTrainer`` subclass (before the trainer class):
+
+        class FusedSFTTrainer(FusedCELossMixin, SFTTrainer): ...
+
+    ``compute_loss`` keeps the signature and return convention of
+    ``Trainer.compute_loss`` (SP/transformers/trainer.py:1938-2020) for the default path the
+    reference takes (no label smoother, no custom loss function): the model is called with the
+    inputs plus ``num_items_in_batch``, the loss is read from its outputs and multiplied by the
+    number of processes to cancel DDP's gradient averaging (:2013-2019).  On the first call with a
+    DDP-wrapped model it also registers the gradient communication hook (seam #2), because
+    ``accelerator.prepare`` wraps the model only inside ``train()`` (trainer.py:1463,1607).
+    """
+
+    b200sft_flags: int = 0
+    b200sft_chunk_rows: int = 0
+    b200sft_register_comm_hook: bool = True
+
+    def _b200sft_prepare(self, model: nn.Module) -> None:
+        inner = _unwrap(model)
+        if not isinstance(getattr(inner, "lm_head", None), FusedLMHead):
+            install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_rows)
+        if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)
+                and not getattr(model, "_b200sft_hook", False)):
+            from .comm_hook import register_b200_comm_hook
+
+            register_b200_comm_hook(model)
+            model._b200sft_hook = True
+
+    def _b200sft_num_processes(self) -> int:
+        acc = getattr(self, "accelerator", None)
+        if acc is not None:
+            return int(acc.num_processes)
+        return int(getattr(self, "num_processes", 1))
+
+    def compute_loss(self, model: nn.Module, inputs: dict, return_outputs: bool = False,
+                     num_items_in_batch: Optional[Union[torch.Tensor, int]] = None
+                     ) -> Union[torch.Tensor, Tuple[torch.Tensor, Any]]:
+        if getattr(self, "label_smoother", None) is not None or getattr(self, "compute_loss_func", None) is not None:
+            # not the reference's configuration; leave those paths to the stock implementation
+            return super().compute_loss(model, inputs, return_outputs=return_outputs,
+                                        num_items_in_batch=num_items_in_batch)
+        self._b200sft_prepare(model)
+        kwargs = {}
+        if num_items_in_batch is not None and getattr(self, "model_accepts_loss_kwargs", True):
+            kwargs["num_items_in_batch"] = num_items_in_batch
+        with fused_head_armed(model):
+            outputs = model(**{**inputs, **kwargs})
+        if isinstance(outputs, dict) and "loss" not in outputs:
+            raise ValueError(
+                "The model did not return a loss from the inputs, only the following keys: "
+                f"{','.join(outputs.keys())}. For reference, the inputs it received are {','.join(inputs.keys())}."
+            )
+        loss = outputs["loss"] if isinstance(outputs, dict) else outputs[0]
+        args = getattr(self, "args", None)
+        average = getattr(args, "average_tokens_across_devices", True)
+        if average and num_items_in_batch is not None and getattr(self, "model_accepts_loss_kwargs", True):
+            loss = loss * self._b200sft_num_processes()
+        if return_outputs:
+            # the fused path never forms logits: hand back outputs with logits cleared so that a
+            # caller that expects them fails visibly instead of reading hidden states
+            if hasattr(outputs, "logits"):
+                outputs.logits = None
+            return loss, outputs
+        return loss

@@ -17,6 +17,39 @@ from ._cabi import DENOM_DEVICE, DENOM_NONE, DENOM_VALID, FLAG_ROUND_LOGITS_BF16
 
 IGNORE_INDEX = -100  # torch.nn.functional.cross_entropy default, SP/transformers/loss/loss_utils.py:28
 
+
+class _Stats:
+    """Bookkeeping for bench.py: how many of this library's kernels were launched, and (when
+    ``events`` is a dict) CUDA-event pairs around the fused calls on their launch stream."""
+
+    def __init__(self):
+        self.kernel_launches = 0
+        self.events = None  # None = off; else {"flce_fwd": [(start, end), ...], ...}
+
+    def reset(self, with_events: bool = False):
+        self.kernel_launches = 0
+        self.events = {} if with_events else None
+
+    def begin(self, name: str, device):
+        if self.events is None:
+            return None
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record(torch.cuda.current_stream(device))
+        self.events.setdefault(name, []).append(ev)
+        return ev
+
+    def end(self, ev, device):
+        if ev is not None:
+            ev[1].record(torch.cuda.current_stream(device))
+
+    def mean_ms(self, name: str) -> float:
+        evs = (self.events or {}).get(name, [])
+        return sum(a.elapsed_time(b) for a, b in evs) / len(evs) if evs else float("nan")
+
+
+STATS = _Stats()
+BWD_DEFAULT_CHUNK_ROWS = 4096  # keep in sync with DEFAULT_CHUNK_ROWS in csrc/flce.cu (launch counting only)
+
 __all__ = [
     "label_prep", "flce_forward", "flce_backward", "gemm_bf16", "scale_", "scale_cast_f32_to_bf16",
     "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX", "FLAG_ROUND_LOGITS_BF16",
@@ -58,6 +91,7 @@ def label_prep(labels: torch.Tensor, ignore_index: int = IGNORE_INDEX) -> Tuple[
         lib = _cabi.load()
         check(lib.b200sft_label_prep(_ptr(labels), B, T, ignore_index, _ptr(shifted), _ptr(counts),
                                      _stream_ptr(labels)), "b200sft_label_prep")
+        STATS.kernel_launches += 1 if B * T > 0 else 0
     return shifted, counts
 
 
@@ -103,9 +137,12 @@ def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: 
         loss = torch.empty((), dtype=torch.float32, device=x.device)
         lse = torch.empty(N, dtype=torch.float32, device=x.device)
         n_valid = torch.empty((), dtype=torch.int64, device=x.device)
+        ev = STATS.begin("flce_fwd", x.device)
         check(lib.b200sft_flce_fwd(_ptr(x), _ptr(w), _ptr(labels), N, H, V, ignore_index, float(scale), mode,
                                    _ptr(denom), flags, _ptr(loss), _ptr(lse), _ptr(n_valid), _ptr(ws), ws_bytes,
                                    _stream_ptr(x)), "b200sft_flce_fwd")
+        STATS.end(ev, x.device)
+        STATS.kernel_launches += 3  # GEMM+softmax epilogue, row merge, loss reduce
     return loss, lse, n_valid
 
 
@@ -126,9 +163,14 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
         dx = torch.empty_like(x)
         dw = torch.empty_like(w)
+        ev = STATS.begin("flce_bwd", x.device)
         check(lib.b200sft_flce_bwd(_ptr(x), _ptr(w), _ptr(labels), _ptr(lse), _ptr(grad_out), N, H, V,
                                    ignore_index, float(scale), mode, _ptr(denom), flags, chunk_rows, _ptr(dx),
                                    _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
+        STATS.end(ev, x.device)
+        chunk = chunk_rows if chunk_rows > 0 else BWD_DEFAULT_CHUNK_ROWS
+        chunk = min((chunk + 127) // 128 * 128, (N + 127) // 128 * 128)
+        STATS.kernel_launches += 3 * ((N + chunk - 1) // chunk)  # dlogits, dX, dW GEMMs per row chunk
     return dx, dw
 
 
@@ -170,6 +212,7 @@ def scale_(buf: torch.Tensor, scale: float) -> torch.Tensor:
                   "b200sft_scale_f32_inplace")
         else:
             raise ValueError(f"unsupported bucket dtype {buf.dtype}")
+        STATS.kernel_launches += 1 if buf.numel() > 0 else 0
     return buf
 
 
@@ -184,6 +227,7 @@ def scale_cast_f32_to_bf16(src: torch.Tensor, scale: float, out: Optional[torch.
             out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
         check(lib.b200sft_scale_cast_f32_to_bf16(_ptr(src), _ptr(out), src.numel(), float(scale), _stream_ptr(src)),
               "b200sft_scale_cast_f32_to_bf16")
+        STATS.kernel_launches += 1 if src.numel() > 0 else 0
     return out
 
 
@@ -196,6 +240,7 @@ def cast_bf16_to_f32(src: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -
     with torch.cuda.device(src.device):
         check(lib.b200sft_cast_bf16_to_f32(_ptr(src), _ptr(out), src.numel(), float(scale), _stream_ptr(src)),
               "b200sft_cast_bf16_to_f32")
+        STATS.kernel_launches += 1 if src.numel() > 0 else 0
     return out
 
 

@@ -242,7 +242,10 @@ def run_b200(args) -> dict:
     launches = ops.STATS.kernel_launches
     fwd_ms, bwd_ms = ops.STATS.mean_ms("flce_fwd"), ops.STATS.mean_ms("flce_bwd")
     ops.STATS.reset(with_events=False)
-    ms_e2e, wall_e2e, last_loss = timed(args.steps, e2e=True, first_step=200)
+    if args.no_e2e:
+        ms_e2e, wall_e2e, last_loss = float("nan"), float("nan"), None
+    else:
+        ms_e2e, wall_e2e, last_loss = timed(args.steps, e2e=True, first_step=200)
     clocks = sampler.stop() if rank == 0 else None
 
     tokens_per_step = B * T * GA * world
@@ -376,6 +379,7 @@ def main():
     ap.add_argument("--attn", default="auto")
     ap.add_argument("--cpu-tokens", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus != world and world == 1 and args.gpus > 1:

@@ -11,7 +11,8 @@
  *   - every pointer is a CUDA device pointer on the current device unless marked "host";
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *   - no entry point synchronises the host or allocates device memory: scratch is supplied by the
- *     caller, sized by the matching *_workspace_bytes() query;
+ *     caller, sized by the matching *_workspace_bytes() query (b200sft_flce_fwd_noalloc carries
+ *     its own fixed scratch instead);
  *   - return value 0 = success, negative = error (b200sft_last_error() gives the text);
  *   - bf16 tensors are row-major and 16-byte aligned, with hidden size H and vocabulary V
  *     multiples of 8 (TMA needs 16-byte row pitches).
@@ -73,6 +74,36 @@ int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N,
                      int ignore_index, float scale, int denom_mode, const int64_t* denom, uint32_t flags,
                      float* loss, float* lse, int64_t* n_valid, void* workspace, size_t workspace_bytes,
                      void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Forward, for callers that cannot allocate.  Has no counterpart in the reference.
+ *
+ * b200sft_flce_fwd needs scratch that somebody must allocate.  Some users of this ABI cannot do
+ * that: a ctypes / cgo-style stub that is handed tensors by another framework and owns no device
+ * allocator; a loss or evaluation callback that runs while PyTorch's caching allocator already
+ * holds nearly all of HBM, so a raw cudaMalloc fails; code on the training loop's critical path,
+ * where cudaMalloc / cudaFree would synchronise the whole device and stall the communication
+ * stream that is overlapping backward.  This variant takes the same inputs and outputs, computes
+ * exactly what b200sft_flce_fwd computes with the same kernels, and uses a fixed scratch array
+ * that is part of the library image instead.  It calls no cudaMalloc, cudaFree or any allocating
+ * routine.
+ *
+ * Limit: the call needs b200sft_flce_fwd_workspace_bytes(N,H,V) bytes and is refused with an
+ * error if that exceeds B200SFT_NOALLOC_SCRATCH_BYTES (40 MiB -- enough for 8,192 rows against
+ * the 128,256-token vocabulary, or 16,384 rows against 64k).  Larger batches: call it per row
+ * block, or use b200sft_flce_fwd.  Every GPU that loads the library keeps those 40 MiB reserved
+ * until the process exits.
+ *
+ * The first call on each device looks up the array's device address (with that device current);
+ * make that first call before starting any stream capture.  All calls on a device share the one
+ * array, which still holds the previous call's contents: the call itself clears the part that
+ * must start at zero, but two calls that overlap on the GPU (different streams, no dependency)
+ * race on it -- serialise them.
+ */
+#define B200SFT_NOALLOC_SCRATCH_BYTES (40u << 20)
+int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
+                             int ignore_index, float scale, int denom_mode, const int64_t* denom,
+                             uint32_t flags, float* loss, float* lse, int64_t* n_valid, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Fused LM-head + masked cross-entropy, backward.  Replaces autograd's backward of the three

@@ -13,6 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libb200sft.so"
 
 FLAG_ROUND_LOGITS_BF16 = 1
 DENOM_NONE, DENOM_DEVICE, DENOM_VALID = 0, 1, 2
+NOALLOC_SCRATCH_BYTES = 40 << 20  # B200SFT_NOALLOC_SCRATCH_BYTES
 
 # name -> (restype, argtypes); mirrors include/b200sft.h one to one (checked by tests/test_cabi_symbols.py)
 SIGNATURES = {
@@ -22,6 +23,8 @@ SIGNATURES = {
     "b200sft_flce_fwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "b200sft_flce_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
                                  c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200sft_flce_fwd_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
+                                         c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200sft_flce_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200sft_flce_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                  c_float, c_int, c_void_p, c_uint32, c_int, c_void_p, c_void_p, c_void_p,

@@ -559,3 +559,56 @@ int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// Forward entry point that allocates nothing
+// =============================================================================================
+// Scratch for b200sft_flce_fwd_noalloc lives in the library image itself: every GPU that loads
+// libb200sft.so reserves B200SFT_NOALLOC_SCRATCH_BYTES of HBM for it until the process exits.
+// `g_noalloc_scratch` below is only a host-side handle for that array -- the device address is
+// looked up with cudaGetSymbolAddress, once per device, before the first launch.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200SFT_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// Device address of the scratch array on the current device (resolved on first use per device).
+int noalloc_scratch_ptr(void** out) {
+  int dev = -1;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(B200SFT_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  void* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(B200SFT_ERR_CUDA, "cudaGetSymbolAddress(noalloc scratch) failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);  // racing first calls resolve the same address
+  }
+  *out = p;
+  return B200SFT_OK;
+}
+
+}  // namespace
+
+extern "C" int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
+                                        int ignore_index, float scale, int denom_mode, const int64_t* denom,
+                                        uint32_t flags, float* loss, float* lse, int64_t* n_valid, void* stream) {
+  const size_t need = b200sft_flce_fwd_workspace_bytes(N, H, V);
+  if (need > static_cast<size_t>(B200SFT_NOALLOC_SCRATCH_BYTES))
+    return fail(B200SFT_ERR_WORKSPACE,
+                "b200sft_flce_fwd_noalloc: N=%d x V=%d needs %zu bytes of scratch but the built-in scratch holds %zu; "
+                "split the rows into smaller calls or use b200sft_flce_fwd with caller-provided scratch",
+                N, V, need, static_cast<size_t>(B200SFT_NOALLOC_SCRATCH_BYTES));
+  void* scratch = nullptr;
+  int rc = noalloc_scratch_ptr(&scratch);
+  if (rc != 0) return rc;
+  // Same kernels as b200sft_flce_fwd.  The array keeps whatever the previous call left in it: the
+  // per-tile partials and row losses are fully rewritten for this call's N and V, and the
+  // target-logit slots (the one region that must start at zero) are cleared in-stream by the
+  // forward path itself before the GEMM.
+  return b200sft_flce_fwd(x, w, labels, N, H, V, ignore_index, scale, denom_mode, denom, flags, loss, lse, n_valid,
+                          scratch, static_cast<size_t>(B200SFT_NOALLOC_SCRATCH_BYTES), stream);
+}

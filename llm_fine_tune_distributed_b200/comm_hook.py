@@ -15,8 +15,8 @@ over NVLink 5 / NVSwitch (NVLS when available -- none of the reference's socket-
 overrides, deploy/pytorchjob.yaml:53-64, are set).  The collective itself is ``torch.distributed``
 plumbing (ProcessGroupNCCL).
 """
-from __future__ import annotations
-
+# NB: no `from __future__ import annotations` here -- DDP checks the hook's annotations as objects
+# (bucket: dist.GradBucket, return: torch.futures.Future[torch.Tensor]), distributed.py:2262-2290.
 from typing import Callable, Optional
 
 import torch

@@ -1,0 +1,29 @@
+"""CPU stand-ins for the two CUDA operators, built from the oracle, so that the host-side wiring
+(FusedLMHead, loss_function patch, compute_loss mixin, DDP hook, trainer loop) can be exercised
+without a GPU.  Test-only: the product raises on CPU tensors."""
+import torch
+
+from oracle import sft_oracle as oracle
+
+
+def label_prep(labels, ignore_index=-100):
+    shifted = oracle.shift_labels(labels, ignore_index)
+    counts = torch.tensor([int(labels.ne(ignore_index).sum()), int(shifted.ne(ignore_index).sum())])
+    return shifted.reshape(-1).to(torch.int32), counts
+
+
+def fused_linear_cross_entropy(hidden, weight, shifted_labels, num_items_in_batch=None, scale=1.0,
+                               ignore_index=-100, flags=0, chunk_rows=0):
+    n = None if num_items_in_batch is None else float(num_items_in_batch)
+    return oracle.lm_head_ce(hidden, weight, shifted_labels.long(), n, ignore_index) * scale
+
+
+def install(monkeypatch_or_none=None):
+    from llm_fine_tune_distributed_b200 import ops
+
+    if monkeypatch_or_none is not None:
+        monkeypatch_or_none.setattr(ops, "label_prep", label_prep)
+        monkeypatch_or_none.setattr(ops, "fused_linear_cross_entropy", fused_linear_cross_entropy)
+    else:
+        ops.label_prep = label_prep
+        ops.fused_linear_cross_entropy = fused_linear_cross_entropy

@@ -1,0 +1,128 @@
+"""World-size-2 CPU (gloo) coverage of the multi-GPU path: the comm hook against stock DDP, and
+BASELINE.json config 1 -- the tiny SmolLM3 (2 layers, hidden 256, vocab 128,256) driven by the
+training loop over two ranks.  The CUDA kernels are replaced by oracle stand-ins (there is no CPU
+kernel); everything else -- head swap, loss seam, no_sync windows, num_items across ranks, hook,
+clip, AdamW -- is the product code."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _init(rank, world, port):
+    for p in (ROOT, HERE):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+
+
+def _hook_worker(rank, world, port, ret):
+    _init(rank, world, port)
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    from llm_fine_tune_distributed_b200.comm_hook import B200HookState, b200_allreduce_hook
+
+    def run(use_hook):
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.Tanh(), torch.nn.Linear(256, 32)).to(torch.bfloat16)
+        ddp = DDP(net, bucket_cap_mb=1)
+        state = None
+        if use_hook:
+            state = B200HookState(None, scale_fn=lambda buf, s: buf.mul_(s))  # CPU stand-in for the scale kernel
+            ddp.register_comm_hook(state, b200_allreduce_hook)
+        g = torch.Generator().manual_seed(10 + rank)
+        x = torch.randn(16, 64, generator=g).to(torch.bfloat16)
+        with ddp.no_sync():                       # accumulation micro-batch: the hook must not fire
+            ddp(x).float().pow(2).sum().backward()
+        fired_in_no_sync = state.buckets_seen if state else 0
+        ddp(x * 0.5).float().pow(2).sum().backward()
+        return [p.grad.clone() for p in net.parameters()], fired_in_no_sync, (state.buckets_seen if state else 0)
+
+    stock, _, _ = run(False)
+    ours, fired_early, fired = run(True)
+    same = all(torch.equal(a, b) for a, b in zip(stock, ours))
+    gathered = [torch.zeros_like(ours[0]) for _ in range(world)]
+    dist.all_gather(gathered, ours[0])
+    ret[rank] = (same, fired_early, fired, bool(torch.equal(gathered[0], gathered[1])))
+    dist.destroy_process_group()
+
+
+def test_comm_hook_equals_stock_ddp_gloo_world2():
+    ret = mp.Manager().dict()
+    mp.spawn(_hook_worker, args=(2, 29621, ret), nprocs=2, join=True)
+    for r in range(2):
+        same, fired_early, fired, equal_across = ret[r]
+        assert same, "grads differ from DDP's built-in allreduce"
+        assert fired_early == 0 and fired >= 1
+        assert equal_across
+
+
+def _rows():
+    path = "/root/reference/data/qa_dataset.parquet"
+    from llm_fine_tune_distributed_b200.training import load_qa_rows
+
+    if os.path.exists(path):
+        return load_qa_rows(path)[:64]
+    return [{"full-question": f"For topic {i}, how do I do thing {i}?", "answer": "Carefully. " * (i % 7 + 1)} for i in range(64)]
+
+
+def _train_worker(rank, world, port, ret):
+    _init(rank, world, port)
+    import _cpu_standins
+
+    _cpu_standins.install()
+    from llm_fine_tune_distributed_b200.comm_hook import B200HookState
+    from llm_fine_tune_distributed_b200.loss import install_fused_head
+    from llm_fine_tune_distributed_b200.training import (ByteChatTokenizer, MiniSFTTrainer, SFTSettings, ShardedBatches,
+                                                         apply_freeze_policy, format_prompt, make_model)
+
+    torch.manual_seed(0)
+    model = make_model("tiny", torch.device("cpu"), attn="eager")
+    apply_freeze_policy(model)
+    install_fused_head(model)
+    tok = ByteChatTokenizer(model.config.vocab_size)
+    tokens = [tok.apply_chat_template(format_prompt(r)["messages"]) for r in _rows()]
+    args = SFTSettings(per_device_train_batch_size=2, gradient_accumulation_steps=2, max_steps=2, max_seq_length=48,
+                       gradient_checkpointing=False, learning_rate=1e-3, logging_steps=1)
+    batches = ShardedBatches(tokens, 2, rank, world, tok.pad_token_id, args.max_seq_length, seed=42)
+    state = B200HookState(None, scale_fn=lambda buf, s: buf.mul_(s))
+    logs = []
+
+    class Log:
+        def on_log(self, l):
+            logs.append(dict(l))
+
+    trainer = MiniSFTTrainer(model, args, batches, callbacks=[Log()], device=torch.device("cpu"), comm_hook_state=state)
+    w0 = model.lm_head.weight.detach().clone()
+    res = trainer.train()
+    w1 = model.lm_head.weight.detach().float()
+    gathered = [torch.zeros_like(w1) for _ in range(world)]
+    dist.all_gather(gathered, w1)
+    ret[rank] = dict(steps=res.global_step, loss=res.training_loss, logs=logs, buckets=state.buckets_seen,
+                     replicas_equal=bool(torch.equal(gathered[0], gathered[1])),
+                     moved=bool((w1 != w0.float()).any()), tokens=res.tokens_seen)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_config1_tiny_smollm3_sft_gloo_world2():
+    ret = mp.Manager().dict()
+    mp.spawn(_train_worker, args=(2, 29631, ret), nprocs=2, join=True)
+    r0, r1 = ret[0], ret[1]
+    assert r0["steps"] == r1["steps"] == 2
+    assert r0["replicas_equal"] and r1["replicas_equal"], "replicas diverged: gradient allreduce is broken"
+    assert r0["moved"]
+    # the hook fires only on the last micro-batch of each window: same bucket count per step on both ranks
+    assert r0["buckets"] == r1["buckets"] and r0["buckets"] >= 2
+    # logged loss is the cross-rank mean (nested_gather(...).mean()), identical on both ranks, near ln(V)
+    assert r0["logs"][0]["loss"] == r1["logs"][0]["loss"]
+    assert 8.0 < r0["logs"][0]["loss"] < 16.0
+    assert r0["tokens"] == r1["tokens"] > 0

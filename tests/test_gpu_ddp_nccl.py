@@ -1,0 +1,72 @@
+"""NCCL, 2 ranks on one box: the comm hook (CUDA scale kernel on the side stream + NCCL allreduce)
+must give exactly the gradients stock DDP gives, including under no_sync accumulation, and the
+fp32 compress variant must match torch's bf16_compress_hook.  Skipped with fewer than two GPUs."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, ret):
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, b200_allreduce_hook,
+                                                          b200_bf16_compress_hook)
+
+    def run(dtype, hook):
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(512, 2048), torch.nn.GELU(), torch.nn.Linear(2048, 2048),
+                                  torch.nn.GELU(), torch.nn.Linear(2048, 256)).to(dev).to(dtype)
+        ddp = DDP(net, device_ids=[rank], bucket_cap_mb=2)
+        state = None
+        if hook == "b200":
+            state = B200HookState(None)
+            ddp.register_comm_hook(state, b200_allreduce_hook)
+        elif hook == "b200_compress":
+            state = B200HookState(None)
+            ddp.register_comm_hook(state, b200_bf16_compress_hook)
+        elif hook == "torch_compress":
+            ddp.register_comm_hook(None, default_hooks.bf16_compress_hook)
+        g = torch.Generator().manual_seed(10 + rank)
+        x = torch.randn(64, 512, generator=g).to(dev).to(dtype)
+        for _ in range(2):  # second iteration runs on DDP's rebuilt buckets
+            with ddp.no_sync():
+                ddp(x).float().pow(2).mean().backward()
+            ddp(x * 0.5).float().pow(2).mean().backward()
+        torch.cuda.synchronize()
+        return [p.grad.clone() for p in net.parameters()], state
+
+    out = {}
+    stock, _ = run(torch.bfloat16, None)
+    ours, st = run(torch.bfloat16, "b200")
+    out["bf16_equal"] = all(torch.equal(a, b) for a, b in zip(stock, ours))
+    out["buckets"] = st.buckets_seen
+    ref_c, _ = run(torch.float32, "torch_compress")
+    ours_c, _ = run(torch.float32, "b200_compress")
+    out["compress_equal"] = all(torch.equal(a, b) for a, b in zip(ref_c, ours_c))
+    ret[rank] = out
+    dist.destroy_process_group()
+
+
+def test_comm_hook_nccl_world2_matches_stock_ddp():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(2, 29641, ret), nprocs=2, join=True)
+    for r in range(2):
+        assert ret[r]["bf16_equal"], "bf16 bucket path differs from stock DDP"
+        assert ret[r]["compress_equal"], "fp32 compress path differs from torch's bf16_compress_hook"
+        assert ret[r]["buckets"] >= 2

@@ -1,0 +1,106 @@
+"""Host-side mirror of the reference interface, on CPU: the lm_head swap keeps names, tying and
+unarmed behaviour; compute_loss follows Trainer.compute_loss's conventions; driver helpers follow
+training.py."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import _cpu_standins
+from oracle import sft_oracle as oracle
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def tiny():
+    from transformers import SmolLM3Config, SmolLM3ForCausalLM
+
+    cfg = SmolLM3Config(num_hidden_layers=2, hidden_size=64, intermediate_size=128, num_attention_heads=4,
+                        num_key_value_heads=1, vocab_size=512, max_position_embeddings=128, tie_word_embeddings=True,
+                        pad_token_id=0, bos_token_id=1, eos_token_id=2)
+    cfg._attn_implementation = "eager"
+    torch.manual_seed(0)  # same construction as tests/golden/make_golden.py -> same weights
+    return SmolLM3ForCausalLM(cfg).to(torch.bfloat16).eval()
+
+
+def test_fused_head_keeps_names_tying_and_unarmed_forward(tiny):
+    from llm_fine_tune_distributed_b200 import FusedLMHead, install_fused_head
+
+    ids = torch.randint(0, 512, (2, 8), generator=torch.Generator().manual_seed(1))
+    before = tiny(input_ids=ids).logits
+    keys = list(tiny.state_dict().keys())
+    install_fused_head(tiny)
+    install_fused_head(tiny)  # idempotent
+    assert isinstance(tiny.lm_head, FusedLMHead)
+    assert list(tiny.state_dict().keys()) == keys
+    assert tiny.lm_head.weight is tiny.model.embed_tokens.weight
+    assert torch.equal(tiny(input_ids=ids).logits, before)           # unarmed: an ordinary linear head
+    stock = tiny(input_ids=ids, labels=ids).loss                      # unarmed + labels: stock ForCausalLMLoss
+    assert torch.isfinite(stock)
+
+
+def test_compute_loss_seam_reproduces_trainer_compute_loss(tiny, monkeypatch):
+    """Armed path on CPU (kernels replaced by the oracle stand-ins) vs the golden values produced by
+    the real Trainer.compute_loss: same loss, x num_processes, logits withheld."""
+    from llm_fine_tune_distributed_b200 import FusedCELossMixin, install_fused_head
+
+    _cpu_standins.install(monkeypatch)
+    install_fused_head(tiny)
+    d = np.load(os.path.join(G, "smollm3_tiny_step.npz"))
+
+    class Seam(FusedCELossMixin):
+        num_processes = 2
+        model_accepts_loss_kwargs = True
+        args = None
+
+    seam = Seam()
+    n = torch.tensor(int(d["num_items"]))
+    for i in range(2):
+        inputs = {"input_ids": torch.from_numpy(d[f"input_ids_{i}"]), "labels": torch.from_numpy(d[f"labels_{i}"])}
+        loss, outputs = seam.compute_loss(tiny, inputs, return_outputs=True, num_items_in_batch=n)
+        ref = float(d[f"compute_loss_{i}"])
+        assert abs(float(loss) - ref) <= 1e-6 * abs(ref)
+        assert outputs.logits is None
+    # num_items_in_batch=None -> reduction="mean", no x num_processes (trainer.py:2013-2019)
+    inputs = {"input_ids": torch.from_numpy(d["input_ids_0"]), "labels": torch.from_numpy(d["labels_0"])}
+    loss = seam.compute_loss(tiny, inputs)
+    assert abs(float(loss) - float(d["model_loss_mean_0"])) <= 1e-6 * abs(float(d["model_loss_mean_0"]))
+    assert not tiny.lm_head.armed  # the context manager disarms the head again
+
+
+def test_freeze_policy_matches_reference_counts():
+    """training.py:114-145 on the real 3B config (meta tensors): 418,914,304 of 3,075,098,624
+    parameters trainable (claude.md:242-243 of the reference)."""
+    from transformers import SmolLM3Config, SmolLM3ForCausalLM
+
+    from llm_fine_tune_distributed_b200.training import apply_freeze_policy
+
+    with torch.device("meta"):
+        model = SmolLM3ForCausalLM(SmolLM3Config(tie_word_embeddings=True))
+    model.tie_weights()
+    trainable, total = apply_freeze_policy(model)
+    assert (trainable, total) == (418_914_304, 3_075_098_624)
+    assert model.model.embed_tokens.weight.requires_grad  # tied to lm_head -> backward crosses all layers
+
+
+def test_collate_and_settings(monkeypatch):
+    from llm_fine_tune_distributed_b200.training import ByteChatTokenizer, SFTSettings, collate, format_prompt
+
+    batch = collate([[5, 6, 7], [8, 9, 10, 11, 12, 13]], pad_id=0, max_len=5)
+    assert batch["input_ids"].tolist() == [[5, 6, 7, 0, 0], [8, 9, 10, 11, 12]]
+    assert batch["attention_mask"].tolist() == [[1, 1, 1, 0, 0], [1, 1, 1, 1, 1]]
+    assert batch["labels"].tolist() == [[5, 6, 7, -100, -100], [8, 9, 10, 11, 12]]
+    msgs = format_prompt({"full-question": "q?", "answer": "a."})["messages"]
+    assert [m["role"] for m in msgs] == ["system", "user", "assistant"]
+    ids = ByteChatTokenizer(128256).apply_chat_template(msgs)
+    assert ids[-1] == 1 and max(ids) < 128256
+
+    monkeypatch.setenv("BATCH_SIZE", "28")
+    monkeypatch.setenv("LEARNING_RATE", "1e-4")
+    monkeypatch.setenv("EPOCHS", "2")
+    s = SFTSettings.from_env(world_size=2, local_rank=1)
+    assert s.per_device_train_batch_size == 28 and s.learning_rate == 2e-4  # lr x world, training.py:263
+    assert s.ddp_backend == "nccl" and s.ddp_bucket_cap_mb == 50 and not s.ddp_find_unused_parameters
+    assert s.gradient_accumulation_steps == 4 and s.max_seq_length == 1024 and s.max_grad_norm == 1.0

@@ -50,7 +50,7 @@ def main():
     ap.add_argument("--vocab", type=int, default=128256)
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--chunk-rows", type=int, default=0)
+    ap.add_argument("--chunk-cols", type=int, default=0)
     ap.add_argument("--no-torch", action="store_true")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -79,14 +79,14 @@ def main():
                 out["f"] = ops.flce_forward(x, w, lab32, denom=n_items)
 
             def bwd():
-                out["b"] = ops.flce_backward(x, w, lab32, out["f"][1], g, denom=n_items, chunk_rows=args.chunk_rows)
+                out["b"] = ops.flce_backward(x, w, lab32, out["f"][1], g, denom=n_items, chunk_cols=args.chunk_cols)
 
             t_f = time_ms(fwd, args.iters, args.warmup, flush)
             t_b = time_ms(bwd, args.iters, args.warmup, flush)
             fused_mem = torch.cuda.max_memory_allocated() - base_mem
             fl_f, fl_fb = 2.0 * N * H * V, 6.0 * N * H * V
             rec = {
-                "N": N, "H": H, "V": V, "masked": m, "chunk_rows": args.chunk_rows,
+                "N": N, "H": H, "V": V, "masked": m, "chunk_cols": args.chunk_cols,
                 "fused_fwd_ms": round(t_f, 4), "fused_bwd_ms": round(t_b, 4),
                 "fused_fwd_tflops": round(fl_f / t_f / 1e9, 1),
                 "fused_fwd_bwd_tflops": round(fl_fb / (t_f + t_b) / 1e9, 1),

@@ -110,17 +110,19 @@ int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels
  * calls above (nll_loss_backward, log_softmax_backward, the fp32->bf16 cast of dlogits and the two
  * cuBLAS GEMMs dX = dlogits.W, dW = dlogits^T.X).  dlogits = (softmax - onehot) * grad_out * scale
  * / denom on valid rows, 0 on ignored rows, rounded to bf16 exactly where the reference rounds;
- * it only ever exists as a [chunk_rows,V] bf16 scratch tile set, never as an [N,V] tensor.
+ * it only ever exists as one [N, chunk_cols] bf16 slab of vocabulary columns at a time, never as
+ * an [N,V] tensor; dW slabs are final after one pass, dX accumulates in fp32 across slabs.
  *   lse       [N] fp32 from the forward call
  *   grad_out  fp32 scalar (device): upstream gradient of `loss`
  *   dx        [N,H] bf16 out
  *   dw        [V,H] bf16 out (overwritten)
- *   chunk_rows  rows of dlogits held in scratch at a time (multiple of 128; 0 = library default)
+ *   chunk_cols  vocabulary columns of dlogits held in scratch at a time (rounded up to a multiple
+ *               of 256; 0 = library default: about 1 GiB of scratch, split into equal slabs)
  */
-size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_rows);
+size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols);
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse,
                      const float* grad_out, int N, int H, int V, int ignore_index, float scale,
-                     int denom_mode, const int64_t* denom, uint32_t flags, int chunk_rows, void* dx, void* dw,
+                     int denom_mode, const int64_t* denom, uint32_t flags, int chunk_cols, void* dx, void* dw,
                      void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -5,10 +5,12 @@
 // Forward:  logits tile = X[128 rows] . W[256 vocab rows]^T accumulates in TMEM; the epilogue
 //           folds it into a per-row (max, sum-exp) partial and picks the target logit.  A row-wise
 //           kernel merges the per-vocab-tile partials into lse[N]; one block sums the loss.
-// Backward: per chunk of rows, the same GEMM is recomputed and its epilogue emits
-//           dlogits = (exp(z - lse) - onehot) * coef as bf16 into scratch; two more engine GEMMs
-//           produce dX = dlogits . W and dW = dlogits^T . X reading W, X and the scratch through
-//           MN-major descriptors (no transposes in HBM).
+// Backward: per slab of vocabulary columns, the same GEMM is recomputed and its epilogue emits
+//           dlogits = (exp(z - lse) - onehot) * coef as bf16 into an [N, slab] scratch; two more
+//           engine GEMMs produce dX (+)= dlogits . W[slab] and dW[slab] = dlogits^T . X, reading W,
+//           X and the scratch through MN-major descriptors (no transposes in HBM).  Slabbing V
+//           rather than N makes every dW slab final after one GEMM; only the small dX [N,H]
+//           accumulates (fp32) across slabs.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -102,13 +104,14 @@ struct DlogitsEpi {
     float scale;
     int ignore_index;
     int round_bf16;
-    __nv_bfloat16* out;  // [M][ld]
+    __nv_bfloat16* out;  // [M][ld]: this vocabulary slab of dlogits
     int ld;
+    int col_offset;  // first vocabulary column of the slab (labels are global column indices)
   };
   const Params& p;
   const int M, N;
   float coef_all, coef, lse2;
-  int lbl, row;
+  int lbl, row;  // lbl is slab-local: label - col_offset (never matches when outside the slab)
 
   __device__ DlogitsEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {
     float c = __ldg(p.grad_out) * p.scale;
@@ -118,20 +121,21 @@ struct DlogitsEpi {
 
   __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) {
     row = tc.m0 + row_in_tile;
-    lbl = p.ignore_index;
+    int glbl = p.ignore_index;
     lse2 = 0.f;
     if (row < M) {
-      lbl = __ldg(p.labels + row);
+      glbl = __ldg(p.labels + row);
       lse2 = __ldg(p.lse + row) * LOG2E;
     }
-    coef = (lbl != p.ignore_index) ? coef_all : 0.f;
+    coef = (glbl != p.ignore_index) ? coef_all : 0.f;
+    lbl = glbl - p.col_offset;
   }
 
   __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
     const int col0 = tc.n0 + c;
     if (col0 >= N || row >= M) return;
     float g[32];
-    if (coef == 0.f && lbl == p.ignore_index) {
+    if (coef == 0.f) {  // ignored row (or zero upstream gradient): exact zeros
 #pragma unroll
       for (int j = 0; j < 32; ++j) g[j] = 0.f;
     } else {
@@ -354,6 +358,11 @@ int num_sms() {
   return sms[dev] > 0 ? sms[dev] : 148;
 }
 
+// Rasterisation group for the M-fastest (logit) GEMMs: 64 tiles = 8192 rows of X (33.5 MB at
+// H = 2048) stay L2-resident while every vocabulary tile is swept over them; W is re-streamed
+// once per group.  Without it N = 65536 re-reads all of X from HBM for each of the 501 W panels.
+constexpr int GROUP_M_TILES = 64;
+
 template <class Epi, bool A_MN, bool B_MN>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
                 const typename Epi::Params& ep, cudaStream_t stream) {
@@ -370,6 +379,7 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.tiles_m = (M + BLOCK_M - 1) / BLOCK_M;
   s.tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
   s.m_fastest = m_fastest;
+  s.group_m = s.tiles_m < GROUP_M_TILES ? s.tiles_m : GROUP_M_TILES;
   auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
   B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
@@ -381,13 +391,23 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-constexpr int DEFAULT_CHUNK_ROWS = 4096;
+// Backward stages dlogits one vocabulary slab at a time: [N][slab_cols] bf16.  The default slab
+// width keeps that scratch within ~1 GiB and splits V into equal slabs (multiples of 256 columns).
+constexpr size_t DEFAULT_DLOGITS_SCRATCH_BYTES = size_t(1) << 30;
 
-int resolve_chunk_rows(int N, int chunk_rows) {
-  int c = chunk_rows > 0 ? chunk_rows : DEFAULT_CHUNK_ROWS;
-  c = (c + BLOCK_M - 1) / BLOCK_M * BLOCK_M;
-  const int n_up = (N + BLOCK_M - 1) / BLOCK_M * BLOCK_M;
-  return c < n_up ? c : n_up;
+int resolve_slab_cols(int N, int V, int chunk_cols) {
+  const int v_up = (V + BLOCK_N - 1) / BLOCK_N * BLOCK_N;
+  long long cmax;
+  if (chunk_cols > 0) {
+    cmax = (static_cast<long long>(chunk_cols) + BLOCK_N - 1) / BLOCK_N * BLOCK_N;
+  } else {
+    cmax = static_cast<long long>(DEFAULT_DLOGITS_SCRATCH_BYTES / (2ull * static_cast<size_t>(N))) / BLOCK_N * BLOCK_N;
+    if (cmax < BLOCK_N) cmax = BLOCK_N;
+  }
+  if (cmax >= v_up) return V;  // one slab: no dX accumulation needed
+  const int slabs = static_cast<int>((v_up + cmax - 1) / cmax);
+  const int c = ((v_up + slabs - 1) / slabs + BLOCK_N - 1) / BLOCK_N * BLOCK_N;  // balanced
+  return c;
 }
 
 int check_dims(int N, int H, int V) {
@@ -459,17 +479,17 @@ int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N,
   return B200SFT_OK;
 }
 
-size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_rows) {
+size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols) {
   if (N <= 0 || H <= 0 || V <= 0) return 0;
-  const int c = resolve_chunk_rows(N, chunk_rows);
-  size_t b = align_up(static_cast<size_t>(c) * V * sizeof(__nv_bfloat16), 1024);  // dlogits chunk
-  if (c < N) b += align_up(static_cast<size_t>(V) * H * sizeof(float), 1024);     // fp32 dW accumulator
+  const int c = resolve_slab_cols(N, V, chunk_cols);
+  size_t b = align_up(static_cast<size_t>(N) * c * sizeof(__nv_bfloat16), 1024);  // dlogits slab
+  if (c < V) b += align_up(static_cast<size_t>(N) * H * sizeof(float), 1024);     // fp32 dX accumulator
   return b;
 }
 
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse, const float* grad_out,
                      int N, int H, int V, int ignore_index, float scale, int denom_mode, const int64_t* denom,
-                     uint32_t flags, int chunk_rows, void* dx, void* dw, void* workspace, size_t workspace_bytes,
+                     uint32_t flags, int chunk_cols, void* dx, void* dw, void* workspace, size_t workspace_bytes,
                      void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   int rc = check_dims(N, H, V);
@@ -481,62 +501,64 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
                 "denom_mode DEVICE");
   if (denom_mode == B200SFT_DENOM_DEVICE && denom == nullptr)
     return fail(B200SFT_ERR_INVALID, "denom_mode DEVICE needs a denom pointer");
-  const size_t need = b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_rows);
+  const size_t need = b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_cols);
   if (workspace == nullptr || workspace_bytes < need)
     return fail(B200SFT_ERR_WORKSPACE, "flce_bwd workspace too small: have %zu, need %zu", workspace_bytes, need);
 
-  const int chunk = resolve_chunk_rows(N, chunk_rows);
-  const int num_chunks = (N + chunk - 1) / chunk;
+  const int slab = resolve_slab_cols(N, V, chunk_cols);
+  const int num_slabs = (V + slab - 1) / slab;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   __nv_bfloat16* dlog = reinterpret_cast<__nv_bfloat16*>(ws);
-  ws += align_up(static_cast<size_t>(chunk) * V * sizeof(__nv_bfloat16), 1024);
-  float* dw_acc = (num_chunks > 1) ? reinterpret_cast<float*>(ws) : nullptr;
+  ws += align_up(static_cast<size_t>(N) * slab * sizeof(__nv_bfloat16), 1024);
+  float* dx_acc = (num_slabs > 1) ? reinterpret_cast<float*>(ws) : nullptr;
 
-  const __nv_bfloat16* xb = static_cast<const __nv_bfloat16*>(x);
-  __nv_bfloat16* dxb = static_cast<__nv_bfloat16*>(dx);
+  const __nv_bfloat16* wb = static_cast<const __nv_bfloat16*>(w);
+  __nv_bfloat16* dwb = static_cast<__nv_bfloat16*>(dw);
 
-  for (int ci = 0; ci < num_chunks; ++ci) {
-    const int r0 = ci * chunk;
-    const int rows = (N - r0) < chunk ? (N - r0) : chunk;
-    const __nv_bfloat16* xc = xb + static_cast<size_t>(r0) * H;
+  for (int si = 0; si < num_slabs; ++si) {
+    const int v0 = si * slab;
+    const int cols = (V - v0) < slab ? (V - v0) : slab;
+    const __nv_bfloat16* ws_rows = wb + static_cast<size_t>(v0) * H;  // W[v0 : v0+cols, :]
 
-    // (1) dlogits[rows,V] = (softmax(Xc.W^T) - onehot) * coef   (recompute, epilogue-fused)
+    // (1) dlogits[N,cols] = (softmax(X.W^T)[:, v0:v0+cols] - onehot) * coef   (recompute, epilogue-fused)
     DlogitsEpi::Params dp;
-    dp.labels = labels + r0;
-    dp.lse = lse + r0;
+    dp.labels = labels;
+    dp.lse = lse;
     dp.grad_out = grad_out;
     dp.denom = (denom_mode == B200SFT_DENOM_DEVICE) ? denom : nullptr;
     dp.scale = scale;
     dp.ignore_index = ignore_index;
     dp.round_bf16 = (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0;
     dp.out = dlog;
-    dp.ld = V;
-    rc = launch_gemm<DlogitsEpi, false, false>(xc, H, w, H, rows, V, H, /*m_fastest=*/1, dp, stream);
+    dp.ld = slab;
+    dp.col_offset = v0;
+    rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream);
     if (rc != 0) return rc;
 
-    // (2) dX[rows,H] = dlogits[rows,V] . W[V,H]      A K-major (V contiguous), B = W read MN-major
+    // (2) dX[N,H] (+)= dlogits[N,cols] . W[v0:v0+cols, :]     A K-major, B = W rows read MN-major
     StoreEpi::Params sx;
-    sx.out = dxb + static_cast<size_t>(r0) * H;
-    sx.acc = nullptr;
+    sx.out = static_cast<__nv_bfloat16*>(dx);
+    sx.acc = dx_acc;
     sx.ld = H;
-    sx.mode = STORE_BF16;
-    rc = launch_gemm<StoreEpi, false, true>(dlog, V, w, H, rows, H, V, /*m_fastest=*/0, sx, stream);
+    if (num_slabs == 1)
+      sx.mode = STORE_BF16;
+    else if (si == 0)
+      sx.mode = STORE_F32;
+    else if (si == num_slabs - 1)
+      sx.mode = ACCUM_F32_OUT_BF16;
+    else
+      sx.mode = ACCUM_F32;
+    rc = launch_gemm<StoreEpi, false, true>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream);
     if (rc != 0) return rc;
 
-    // (3) dW[V,H] (+)= dlogits^T[V,rows] . Xc[rows,H]   both operands read MN-major
+    // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every
+    //     row, so each dW slab is final after one GEMM (no accumulation across slabs)
     StoreEpi::Params sw;
-    sw.out = static_cast<__nv_bfloat16*>(dw);
-    sw.acc = dw_acc;
+    sw.out = dwb + static_cast<size_t>(v0) * H;
+    sw.acc = nullptr;
     sw.ld = H;
-    if (num_chunks == 1)
-      sw.mode = STORE_BF16;
-    else if (ci == 0)
-      sw.mode = STORE_F32;
-    else if (ci == num_chunks - 1)
-      sw.mode = ACCUM_F32_OUT_BF16;
-    else
-      sw.mode = ACCUM_F32;
-    rc = launch_gemm<StoreEpi, true, true>(dlog, V, xc, H, V, H, rows, /*m_fastest=*/0, sw, stream);
+    sw.mode = STORE_BF16;
+    rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream);
     if (rc != 0) return rc;
   }
   return B200SFT_OK;

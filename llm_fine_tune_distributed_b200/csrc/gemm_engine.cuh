@@ -35,6 +35,8 @@ struct GemmShape {
   int M, N, K;
   int tiles_m, tiles_n;
   int m_fastest;  // tile order: 1 = consecutive CTAs walk M for a fixed N tile (shares the B panel in L2)
+  int group_m;    // m_fastest only: M tiles per rasterisation group.  All N tiles of a group are finished
+                  // before the next group starts, so the group's A rows stay resident in L2.
 };
 
 struct TileCoord {
@@ -44,8 +46,13 @@ struct TileCoord {
 __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
   TileCoord c;
   if (s.m_fastest) {
-    c.tile_m = tile % s.tiles_m;
-    c.tile_n = tile / s.tiles_m;
+    const int per_group = s.group_m * s.tiles_n;
+    const int g = tile / per_group;
+    const int r = tile - g * per_group;
+    const int left = s.tiles_m - g * s.group_m;
+    const int gm = left < s.group_m ? left : s.group_m;  // the last group may be short
+    c.tile_m = g * s.group_m + r % gm;
+    c.tile_n = r / gm;
   } else {
     c.tile_n = tile % s.tiles_n;
     c.tile_m = tile / s.tiles_n;

@@ -62,7 +62,7 @@ def _unwrap(model: nn.Module) -> nn.Module:
     return model
 
 
-def install_fused_head(model: nn.Module, flags: int = 0, chunk_rows: int = 0) -> nn.Module:
+def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0) -> nn.Module:
     """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model."""
     inner = _unwrap(model)
     head = getattr(inner, "lm_head", None)
@@ -75,7 +75,7 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_rows: int = 0) ->
 
     def loss_function(logits, labels, vocab_size=None, **kwargs):
         if head.armed:
-            return fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_rows=chunk_rows, **kwargs)
+            return fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_cols=chunk_cols, **kwargs)
         return stock_loss(logits=logits, labels=labels, vocab_size=vocab_size, **kwargs)
 
     if not getattr(inner, "_b200sft_patched", False):
@@ -101,7 +101,7 @@ def fused_head_armed(model: nn.Module):
 def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                          num_items_in_batch: Optional[Union[torch.Tensor, int]] = None,
                          ignore_index: int = -100, shift_labels: Optional[torch.Tensor] = None,
-                         flags: int = 0, chunk_rows: int = 0, **_unused: Any) -> torch.Tensor:
+                         flags: int = 0, chunk_cols: int = 0, **_unused: Any) -> torch.Tensor:
     """``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:45-67) on hidden states.
 
     Same arguments and meaning, except that the first argument holds ``[B,T,H]`` hidden states:
@@ -121,7 +121,7 @@ def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labe
         h2 = h2.to(torch.bfloat16)
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     return ops.fused_linear_cross_entropy(h2.contiguous(), w.contiguous(), shifted, num_items_in_batch,
-                                          ignore_index=ignore_index, flags=flags, chunk_rows=chunk_rows)
+                                          ignore_index=ignore_index, flags=flags, chunk_cols=chunk_cols)
 
 
 class FusedCELossMixin:
@@ -139,13 +139,13 @@ class FusedCELossMixin:
     """
 
     b200sft_flags: int = 0
-    b200sft_chunk_rows: int = 0
+    b200sft_chunk_cols: int = 0
     b200sft_register_comm_hook: bool = True
 
     def _b200sft_prepare(self, model: nn.Module) -> None:
         inner = _unwrap(model)
         if not isinstance(getattr(inner, "lm_head", None), FusedLMHead):
-            install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_rows)
+            install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_cols)
         if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)
                 and not getattr(model, "_b200sft_hook", False)):
             from .comm_hook import register_b200_comm_hook

@@ -48,7 +48,18 @@ class _Stats:
 
 
 STATS = _Stats()
-BWD_DEFAULT_CHUNK_ROWS = 4096  # keep in sync with DEFAULT_CHUNK_ROWS in csrc/flce.cu (launch counting only)
+
+
+def _bwd_num_slabs(N: int, V: int, chunk_cols: int) -> int:
+    """Mirror of resolve_slab_cols() in csrc/flce.cu -- used only to count kernel launches."""
+    v_up = (V + 255) // 256 * 256
+    cmax = (chunk_cols + 255) // 256 * 256 if chunk_cols > 0 else max(((1 << 30) // (2 * N)) // 256 * 256, 256)
+    if cmax >= v_up:
+        return 1
+    slabs = (v_up + cmax - 1) // cmax
+    c = ((v_up + slabs - 1) // slabs + 255) // 256 * 256
+    return (V + c - 1) // c
+
 
 __all__ = [
     "label_prep", "flce_forward", "flce_backward", "gemm_bf16", "scale_", "scale_cast_f32_to_bf16",
@@ -148,7 +159,7 @@ def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: 
 
 def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                   grad_out: torch.Tensor, scale: float = 1.0, denom: Optional[torch.Tensor] = None,
-                  ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_rows: int = 0
+                  ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0
                   ) -> Tuple[torch.Tensor, torch.Tensor]:
     """dx [N,H] bf16, dw [V,H] bf16 for the loss produced by :func:`flce_forward`."""
     N, H, V = _check_flce_inputs(x, w, labels)
@@ -159,18 +170,16 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
     mode = DENOM_DEVICE if denom is not None else DENOM_NONE
     lib = _cabi.load()
     with torch.cuda.device(x.device):
-        ws_bytes = lib.b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_rows)
+        ws_bytes = lib.b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_cols)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
         dx = torch.empty_like(x)
         dw = torch.empty_like(w)
         ev = STATS.begin("flce_bwd", x.device)
         check(lib.b200sft_flce_bwd(_ptr(x), _ptr(w), _ptr(labels), _ptr(lse), _ptr(grad_out), N, H, V,
-                                   ignore_index, float(scale), mode, _ptr(denom), flags, chunk_rows, _ptr(dx),
+                                   ignore_index, float(scale), mode, _ptr(denom), flags, chunk_cols, _ptr(dx),
                                    _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
         STATS.end(ev, x.device)
-        chunk = chunk_rows if chunk_rows > 0 else BWD_DEFAULT_CHUNK_ROWS
-        chunk = min((chunk + 127) // 128 * 128, (N + 127) // 128 * 128)
-        STATS.kernel_launches += 3 * ((N + chunk - 1) // chunk)  # dlogits, dX, dW GEMMs per row chunk
+        STATS.kernel_launches += 3 * _bwd_num_slabs(N, V, chunk_cols)  # dlogits, dX, dW GEMMs per vocabulary slab
     return dx, dw
 
 
@@ -263,24 +272,24 @@ def _(x, w, labels, scale, denom, reduction_mean, ignore_index, flags):
 @torch.library.custom_op("b200sft::flce_bwd", mutates_args=())
 def _flce_bwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                  grad_out: torch.Tensor, scale: float, denom: Optional[torch.Tensor], ignore_index: int,
-                 flags: int, chunk_rows: int) -> Tuple[torch.Tensor, torch.Tensor]:
-    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_rows)
+                 flags: int, chunk_cols: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols)
 
 
 @_flce_bwd_op.register_fake
-def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_rows):
+def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols):
     return torch.empty_like(x), torch.empty_like(w)
 
 
 class _FusedLinearCrossEntropy(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_rows):
+    def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_cols):
         loss, lse, n_valid = torch.ops.b200sft.flce_fwd(x, w, labels, scale, denom, reduction_mean, ignore_index,
                                                         flags)
         # reduction="mean" divides by the local valid count; backward takes it as a device scalar
         bwd_denom = n_valid if reduction_mean else denom
         ctx.save_for_backward(x, w, labels, lse, bwd_denom)
-        ctx.scale, ctx.ignore_index, ctx.flags, ctx.chunk_rows = scale, ignore_index, flags, chunk_rows
+        ctx.scale, ctx.ignore_index, ctx.flags, ctx.chunk_cols = scale, ignore_index, flags, chunk_cols
         ctx.mark_non_differentiable(lse, n_valid)
         return loss, lse, n_valid
 
@@ -288,13 +297,13 @@ class _FusedLinearCrossEntropy(torch.autograd.Function):
     def backward(ctx, grad_loss, _g_lse, _g_nvalid):
         x, w, labels, lse, bwd_denom = ctx.saved_tensors
         dx, dw = torch.ops.b200sft.flce_bwd(x, w, labels, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
-                                            ctx.flags, ctx.chunk_rows)
+                                            ctx.flags, ctx.chunk_cols)
         return dx, dw, None, None, None, None, None, None, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,
                                num_items_in_batch: Optional[torch.Tensor] = None, scale: float = 1.0,
-                               ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_rows: int = 0
+                               ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0
                                ) -> torch.Tensor:
     """Differentiable ``cross_entropy(hidden @ weight.T, shifted_labels)`` without the logits.
 
@@ -309,5 +318,5 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shift
             num_items_in_batch = torch.tensor(int(num_items_in_batch), dtype=torch.int64, device=hidden.device)
         denom = num_items_in_batch.to(device=hidden.device, dtype=torch.int64).reshape(())
     loss, _, _ = _FusedLinearCrossEntropy.apply(hidden, weight, shifted_labels, float(scale), denom,
-                                                num_items_in_batch is None, ignore_index, flags, chunk_rows)
+                                                num_items_in_batch is None, ignore_index, flags, chunk_cols)
     return loss

@@ -13,7 +13,7 @@ def label_prep(labels, ignore_index=-100):
 
 
 def fused_linear_cross_entropy(hidden, weight, shifted_labels, num_items_in_batch=None, scale=1.0,
-                               ignore_index=-100, flags=0, chunk_rows=0):
+                               ignore_index=-100, flags=0, chunk_cols=0):
     n = None if num_items_in_batch is None else float(num_items_in_batch)
     return oracle.lm_head_ce(hidden, weight, shifted_labels.long(), n, ignore_index) * scale
 

@@ -41,12 +41,12 @@ def test_version_and_workspace_queries(lib):
     need = lib.b200sft_flce_fwd_workspace_bytes(8192, 2048, 128256)
     assert need == 501 * 8192 * 8 + 2 * 8192 * 4
     assert lib.b200sft_flce_fwd_workspace_bytes(0, 2048, 128256) == 0
-    # backward: one 4096-row dlogits chunk (+ fp32 dW accumulator when N spans several chunks)
-    one = lib.b200sft_flce_bwd_workspace_bytes(4096, 2048, 128256, 0)
-    two = lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 0)
+    # backward: one [N, slab] bf16 dlogits slab (+ fp32 dX accumulator when V spans several slabs)
+    one = lib.b200sft_flce_bwd_workspace_bytes(4096, 2048, 128256, 0)       # 1 GiB budget: single slab
+    two = lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 0)       # two slabs of 64256 columns
     assert one == 4096 * 128256 * 2
-    assert two == one + 128256 * 2048 * 4
-    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 8192) == 8192 * 128256 * 2
+    assert two == 8192 * 64256 * 2 + 8192 * 2048 * 4
+    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 128256) == 8192 * 128256 * 2
 
 
 def test_argument_validation_without_launching(lib):

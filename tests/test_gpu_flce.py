@@ -115,8 +115,8 @@ def test_flce_all_rows_ignored(cuda_device):
     assert torch.isnan(loss_mean)
 
 
-def test_flce_chunked_backward_matches_single_chunk(cuda_device):
-    """Row-chunked dlogits scratch (fp32 dW accumulation across chunks) vs one chunk."""
+def test_flce_slabbed_backward_matches_single_slab(cuda_device):
+    """Vocabulary-slabbed dlogits scratch (fp32 dX accumulation across slabs) vs one slab."""
     from llm_fine_tune_distributed_b200 import ops
 
     N, H, V = 640, 128, 1536
@@ -124,11 +124,13 @@ def test_flce_chunked_backward_matches_single_chunk(cuda_device):
     lab = labels.to(torch.int32)
     loss, lse, n_valid = ops.flce_forward(x, w, lab, reduction_mean=True)
     g = torch.ones((), device=cuda_device)
-    dx1, dw1 = ops.flce_backward(x, w, lab, lse, g, denom=n_valid, chunk_rows=1024)
-    dx2, dw2 = ops.flce_backward(x, w, lab, lse, g, denom=n_valid, chunk_rows=256)
-    assert torch.equal(dx1, dx2)
-    assert _cos(dw1, dw2) > 0.99999
-    assert torch.allclose(dw1.float(), dw2.float(), rtol=2.0 ** -7, atol=1e-6)
+    dx1, dw1 = ops.flce_backward(x, w, lab, lse, g, denom=n_valid, chunk_cols=2048)   # one slab (V = 1536)
+    dx2, dw2 = ops.flce_backward(x, w, lab, lse, g, denom=n_valid, chunk_cols=512)    # three slabs
+    dx3, dw3 = ops.flce_backward(x, w, lab, lse, g, denom=n_valid, chunk_cols=1024)   # two balanced slabs of 768
+    for dx, dw in ((dx2, dw2), (dx3, dw3)):
+        assert torch.equal(dw1, dw)            # every dW slab is produced by one GEMM either way
+        assert _cos(dx1, dx) > 0.99999         # dX: fp32 accumulation across slabs, one bf16 rounding
+        assert torch.allclose(dx1.float(), dx.float(), rtol=2.0 ** -7, atol=1e-6)
 
 
 def test_flce_rejects_cpu_tensors():

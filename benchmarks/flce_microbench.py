@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--chunk-cols", type=int, default=0)
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--skip-ignored", action="store_true", help="compact away ignore_index rows first (valid-row compaction)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     peak_tf, _, peak_kind = peaks()
@@ -75,18 +76,30 @@ def main():
             base_mem = torch.cuda.memory_allocated()
             out = {}
 
-            def fwd():
-                out["f"] = ops.flce_forward(x, w, lab32, denom=n_items)
+            if args.skip_ignored:
+                def fwd():
+                    xc, lc, _ri, pos, nl = ops.compact_rows(x, lab32)
+                    out["c"] = (xc, lc, pos, nl)
+                    out["f"] = ops.flce_forward(xc, w, lc, denom=n_items, n_rows=nl)
 
-            def bwd():
-                out["b"] = ops.flce_backward(x, w, lab32, out["f"][1], g, denom=n_items, chunk_cols=args.chunk_cols)
+                def bwd():
+                    xc, lc, pos, nl = out["c"]
+                    dxc, dw = ops.flce_backward(xc, w, lc, out["f"][1], g, denom=n_items, chunk_cols=args.chunk_cols,
+                                                n_rows=nl)
+                    out["b"] = (ops.scatter_rows(dxc, pos), dw)
+            else:
+                def fwd():
+                    out["f"] = ops.flce_forward(x, w, lab32, denom=n_items)
+
+                def bwd():
+                    out["b"] = ops.flce_backward(x, w, lab32, out["f"][1], g, denom=n_items, chunk_cols=args.chunk_cols)
 
             t_f = time_ms(fwd, args.iters, args.warmup, flush)
             t_b = time_ms(bwd, args.iters, args.warmup, flush)
             fused_mem = torch.cuda.max_memory_allocated() - base_mem
             fl_f, fl_fb = 2.0 * N * H * V, 6.0 * N * H * V
             rec = {
-                "N": N, "H": H, "V": V, "masked": m, "chunk_cols": args.chunk_cols,
+                "N": N, "H": H, "V": V, "masked": m, "chunk_cols": args.chunk_cols, "skip_ignored_rows": args.skip_ignored,
                 "fused_fwd_ms": round(t_f, 4), "fused_bwd_ms": round(t_b, 4),
                 "fused_fwd_tflops": round(fl_f / t_f / 1e9, 1),
                 "fused_fwd_bwd_tflops": round(fl_fb / (t_f + t_b) / 1e9, 1),

@@ -65,15 +65,49 @@ int b200sft_label_prep(const int64_t* labels, int B, int T, int64_t ignore_index
  *   w        [V,H] bf16   lm_head.weight (tied to embed_tokens.weight)
  *   labels   [N]   int32  shifted labels; ignore_index rows contribute nothing
  *   denom    int64 scalar (device) used when denom_mode == B200SFT_DENOM_DEVICE, else may be NULL
+ *   n_rows_dev  int32 scalar (device) or NULL: number of live rows (<= N) when x/labels are the
+ *            compacted tensors from b200sft_compact_rows; N is then the capacity.  NULL = all N rows.
  *   loss     fp32 scalar out
- *   lse      [N] fp32 out: log-sum-exp of every row (saved for backward)
+ *   lse      [N] fp32 out: log-sum-exp of every (live) row (saved for backward)
  *   n_valid  int64 scalar out (may be NULL): #rows with label != ignore_index
  */
 size_t b200sft_flce_fwd_workspace_bytes(int N, int H, int V);
 int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
                      int ignore_index, float scale, int denom_mode, const int64_t* denom, uint32_t flags,
-                     float* loss, float* lse, int64_t* n_valid, void* workspace, size_t workspace_bytes,
-                     void* stream);
+                     const int32_t* n_rows_dev, float* loss, float* lse, int64_t* n_valid, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* Same forward, additionally producing the two logits-based training metrics TRL's SFTTrainer logs
+ * ([TRL, not on disk]: mean_token_accuracy and entropy, computed there from outputs.logits) without
+ * logits: n_correct = #valid rows whose target logit is the row maximum (argmax == label; exact
+ * ties count as correct), entropy_sum = sum over valid rows of the softmax entropy
+ * lse - E_p[z].  One extra fused multiply-add per logit in the epilogue.
+ */
+size_t b200sft_flce_fwd_stats_workspace_bytes(int N, int H, int V);
+int b200sft_flce_fwd_stats(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
+                           int ignore_index, float scale, int denom_mode, const int64_t* denom,
+                           uint32_t flags, const int32_t* n_rows_dev, float* loss, float* lse,
+                           int64_t* n_valid, int64_t* n_correct, float* entropy_sum, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Valid-row compaction.  Rows whose label is ignore_index (padding, prompt tokens, the first token
+ * of every packed sample -- SP/transformers/data/data_collator.py:1426-1428) contribute nothing to
+ * the loss or to dW and get a zero dX row (torch: ignore_index in F.cross_entropy), yet the
+ * reference still pays the full [N,V] GEMMs for them.  b200sft_compact_rows gathers the live rows
+ * so that flce_fwd / flce_bwd run on them only; b200sft_scatter_rows expands dX back.  The live
+ * count never leaves the device.
+ *   x [N,H] bf16, labels [N] int32                                  in
+ *   xc [N,H] bf16        live rows first (stable order), zero-filled up to the next 128-row boundary
+ *   labels_c [N] int32   their labels, ignore_index beyond the live count
+ *   row_index [N] int32  row_index[j] = original row of compact row j
+ *   pos [N] int32        compact position of each original row, -1 if ignored
+ *   n_live int32 scalar  live row count
+ */
+int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int ignore_index, void* xc,
+                         int32_t* labels_c, int32_t* row_index, int32_t* pos, int32_t* n_live, void* stream);
+/*   dx[r,:] = dxc[pos[r],:] when pos[r] >= 0, else 0 (every row of dx is written). */
+int b200sft_scatter_rows(const void* dxc, const int32_t* pos, int N, int H, void* dx, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Forward, for callers that cannot allocate.  Has no counterpart in the reference.
@@ -118,12 +152,14 @@ int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels
  *   dw        [V,H] bf16 out (overwritten)
  *   chunk_cols  vocabulary columns of dlogits held in scratch at a time (rounded up to a multiple
  *               of 256; 0 = library default: about 1 GiB of scratch, split into equal slabs)
+ *   n_rows_dev  as in b200sft_flce_fwd (compacted inputs; dx is then compact too)
  */
 size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols);
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse,
                      const float* grad_out, int N, int H, int V, int ignore_index, float scale,
-                     int denom_mode, const int64_t* denom, uint32_t flags, int chunk_cols, void* dx, void* dw,
-                     void* workspace, size_t workspace_bytes, void* stream);
+                     int denom_mode, const int64_t* denom, uint32_t flags, int chunk_cols,
+                     const int32_t* n_rows_dev, void* dx, void* dw, void* workspace, size_t workspace_bytes,
+                     void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Plain bf16 GEMM on the same tcgen05 engine: C[M,N] = A * B^T, fp32 accumulate, bf16 out.

@@ -22,12 +22,20 @@ SIGNATURES = {
     "b200sft_label_prep": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p]),
     "b200sft_flce_fwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "b200sft_flce_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
-                                 c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+                                 c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                 c_void_p]),
+    "b200sft_flce_fwd_stats_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "b200sft_flce_fwd_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
+                                       c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200sft_compact_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p]),
+    "b200sft_scatter_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200sft_flce_fwd_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
                                          c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200sft_flce_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200sft_flce_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
-                                 c_float, c_int, c_void_p, c_uint32, c_int, c_void_p, c_void_p, c_void_p,
+                                 c_float, c_int, c_void_p, c_uint32, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_size_t, c_void_p]),
     "b200sft_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_int, c_void_p]),

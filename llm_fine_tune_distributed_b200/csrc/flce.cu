@@ -31,16 +31,21 @@ constexpr float LN2 = 0.6931471805599453f;
 // =============================================================================================
 
 // ---- forward: per-row online softmax statistics over one 256-wide vocabulary tile ------------
+// STATS additionally carries sum exp(z - max) * z, from which the row entropy follows
+// (H = lse - E_p[z]); that is what lets token-accuracy / entropy logging work without logits.
+template <bool STATS>
 struct FwdSoftmaxEpi {
   struct Params {
-    const int32_t* labels;  // [M]
-    float2* partials;       // [tiles_n][M]  (max, sum exp(z - max))
-    float* tgt_logit;       // [M]
+    const int32_t* labels;  // [rows]
+    float2* partials;       // [tiles_n][row_pitch]  (max, sum exp(z - max))
+    float* partials_ez;     // [tiles_n][row_pitch]  sum exp(z - max) * z   (STATS only)
+    float* tgt_logit;       // [rows]
+    int row_pitch;          // row capacity of the scratch arrays (>= live rows)
     int round_bf16;
   };
   const Params& p;
   const int M, N;
-  float run_m, run_s;
+  float run_m, run_s, run_ez;
   int lbl, row;
 
   __device__ FwdSoftmaxEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {}
@@ -49,6 +54,7 @@ struct FwdSoftmaxEpi {
     row = tc.m0 + row_in_tile;
     run_m = -INFINITY;
     run_s = 0.f;
+    run_ez = 0.f;
     lbl = (row < M) ? __ldg(p.labels + row) : -1;
   }
 
@@ -72,14 +78,27 @@ struct FwdSoftmaxEpi {
     const float new_m = fmaxf(run_m, cmax);  // finite: at least one real column in this chunk
     const float nm2 = new_m * LOG2E;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    float t0 = 0.f, t1 = 0.f;
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
-      s0 += ex2_approx(fmaf(z[j + 0], LOG2E, -nm2));
-      s1 += ex2_approx(fmaf(z[j + 1], LOG2E, -nm2));
-      s2 += ex2_approx(fmaf(z[j + 2], LOG2E, -nm2));
-      s3 += ex2_approx(fmaf(z[j + 3], LOG2E, -nm2));
+      const float e0 = ex2_approx(fmaf(z[j + 0], LOG2E, -nm2));
+      const float e1 = ex2_approx(fmaf(z[j + 1], LOG2E, -nm2));
+      const float e2 = ex2_approx(fmaf(z[j + 2], LOG2E, -nm2));
+      const float e3 = ex2_approx(fmaf(z[j + 3], LOG2E, -nm2));
+      s0 += e0;
+      s1 += e1;
+      s2 += e2;
+      s3 += e3;
+      if constexpr (STATS) {  // masked columns hold -inf with e = 0: clamp so 0 * z stays 0
+        t0 = fmaf(e0, fmaxf(z[j + 0], -3.0e38f), t0);
+        t1 = fmaf(e1, fmaxf(z[j + 1], -3.0e38f), t1);
+        t0 = fmaf(e2, fmaxf(z[j + 2], -3.0e38f), t0);
+        t1 = fmaf(e3, fmaxf(z[j + 3], -3.0e38f), t1);
+      }
     }
-    run_s = run_s * ex2_approx((run_m - new_m) * LOG2E) + ((s0 + s1) + (s2 + s3));
+    const float rescale = ex2_approx((run_m - new_m) * LOG2E);
+    run_s = run_s * rescale + ((s0 + s1) + (s2 + s3));
+    if constexpr (STATS) run_ez = run_ez * rescale + (t0 + t1);
     run_m = new_m;
     if (lbl >= col0 && lbl < col0 + 32) {
       float t = 0.f;
@@ -90,7 +109,11 @@ struct FwdSoftmaxEpi {
   }
 
   __device__ __forceinline__ void tile_end(const TileCoord& tc, int) {
-    if (row < M) p.partials[static_cast<size_t>(tc.tile_n) * M + row] = make_float2(run_m, run_s);
+    if (row < M) {
+      const size_t at = static_cast<size_t>(tc.tile_n) * p.row_pitch + row;
+      p.partials[at] = make_float2(run_m, run_s);
+      if constexpr (STATS) p.partials_ez[at] = run_ez;
+    }
   }
 };
 
@@ -107,6 +130,8 @@ struct DlogitsEpi {
     __nv_bfloat16* out;  // [M][ld]: this vocabulary slab of dlogits
     int ld;
     int col_offset;  // first vocabulary column of the slab (labels are global column indices)
+    int rows_alloc;  // rows the scratch holds; rows in [live rows, rows_alloc) are written as zeros
+                     // because the dW GEMM contracts over them in whole 64-row blocks
   };
   const Params& p;
   const int M, N;
@@ -133,9 +158,9 @@ struct DlogitsEpi {
 
   __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
     const int col0 = tc.n0 + c;
-    if (col0 >= N || row >= M) return;
+    if (col0 >= N || row >= p.rows_alloc) return;
     float g[32];
-    if (coef == 0.f) {  // ignored row (or zero upstream gradient): exact zeros
+    if (coef == 0.f) {  // ignored / dead row (or zero upstream gradient): exact zeros
 #pragma unroll
       for (int j = 0; j < 32; ++j) g[j] = 0.f;
     } else {
@@ -251,45 +276,71 @@ struct StoreEpi {
 // =============================================================================================
 
 // Merge the per-vocabulary-tile (max, sumexp) partials of each row into lse, and emit the row's
-// loss term (lse - target logit) or 0 for ignored rows.
-__global__ void flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ tgt_logit,
-                                       const int32_t* __restrict__ labels, int M, int tiles_n, int ignore_index,
-                                       float* __restrict__ lse, float* __restrict__ row_loss) {
+// loss term (lse - target logit) or 0 for ignored rows.  With `partials_ez` also the row's softmax
+// entropy and whether the target holds the row maximum (token accuracy).
+__global__ void flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ partials_ez,
+                                       const float* __restrict__ tgt_logit, const int32_t* __restrict__ labels,
+                                       int rows_cap, const int* __restrict__ n_rows_dev, int tiles_n, int ignore_index,
+                                       float* __restrict__ lse, float* __restrict__ row_loss,
+                                       float* __restrict__ row_entropy, unsigned char* __restrict__ row_correct) {
+  const int M = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= M) return;
   float m = -INFINITY;
-  for (int t = 0; t < tiles_n; ++t) m = fmaxf(m, partials[static_cast<size_t>(t) * M + row].x);
-  float s = 0.f;
+  for (int t = 0; t < tiles_n; ++t) m = fmaxf(m, partials[static_cast<size_t>(t) * rows_cap + row].x);
+  float s = 0.f, ez = 0.f;
   for (int t = 0; t < tiles_n; ++t) {
-    const float2 pr = partials[static_cast<size_t>(t) * M + row];
-    s += pr.y * exp2f((pr.x - m) * LOG2E);
+    const float2 pr = partials[static_cast<size_t>(t) * rows_cap + row];
+    const float f = exp2f((pr.x - m) * LOG2E);
+    s += pr.y * f;
+    if (partials_ez) ez += partials_ez[static_cast<size_t>(t) * rows_cap + row] * f;
   }
   const float l = m + logf(s);
   lse[row] = l;
   const int lbl = labels[row];
-  row_loss[row] = (lbl != ignore_index) ? (l - tgt_logit[row]) : 0.f;
+  const bool valid = lbl != ignore_index;
+  const float tgt = tgt_logit[row];
+  row_loss[row] = valid ? (l - tgt) : 0.f;
+  if (partials_ez) {
+    row_entropy[row] = valid ? (l - ez / s) : 0.f;
+    row_correct[row] = (valid && tgt >= m) ? 1 : 0;  // the target logit is the row maximum
+  }
 }
 
-// One block: fixed-order (deterministic) sum of the row losses and count of valid rows.
-__global__ void flce_reduce_loss_kernel(const float* __restrict__ row_loss, const int32_t* __restrict__ labels,
-                                        int M, int ignore_index, float scale, int denom_mode,
+// One block: fixed-order (deterministic) sums of the row losses / entropies and counts.
+__global__ void flce_reduce_loss_kernel(const float* __restrict__ row_loss, const float* __restrict__ row_entropy,
+                                        const unsigned char* __restrict__ row_correct,
+                                        const int32_t* __restrict__ labels, int rows_cap,
+                                        const int* __restrict__ n_rows_dev, int ignore_index, float scale, int denom_mode,
                                         const int64_t* __restrict__ denom, float* __restrict__ loss,
-                                        int64_t* __restrict__ n_valid) {
+                                        int64_t* __restrict__ n_valid, int64_t* __restrict__ n_correct,
+                                        float* __restrict__ entropy_sum) {
+  const int M = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
   __shared__ double s_sum[1024];
+  __shared__ double s_ent[1024];
   __shared__ int s_cnt[1024];
-  double acc = 0.0;
-  int cnt = 0;
+  __shared__ int s_cor[1024];
+  double acc = 0.0, ent = 0.0;
+  int cnt = 0, cor = 0;
   for (int i = threadIdx.x; i < M; i += blockDim.x) {
     acc += static_cast<double>(row_loss[i]);
     cnt += (labels[i] != ignore_index) ? 1 : 0;
+    if (row_entropy) {
+      ent += static_cast<double>(row_entropy[i]);
+      cor += row_correct[i];
+    }
   }
   s_sum[threadIdx.x] = acc;
+  s_ent[threadIdx.x] = ent;
   s_cnt[threadIdx.x] = cnt;
+  s_cor[threadIdx.x] = cor;
   __syncthreads();
   for (int off = blockDim.x >> 1; off > 0; off >>= 1) {
     if (threadIdx.x < off) {
       s_sum[threadIdx.x] += s_sum[threadIdx.x + off];
+      s_ent[threadIdx.x] += s_ent[threadIdx.x + off];
       s_cnt[threadIdx.x] += s_cnt[threadIdx.x + off];
+      s_cor[threadIdx.x] += s_cor[threadIdx.x + off];
     }
     __syncthreads();
   }
@@ -299,6 +350,86 @@ __global__ void flce_reduce_loss_kernel(const float* __restrict__ row_loss, cons
     if (denom_mode == B200SFT_DENOM_VALID) total = total / static_cast<float>(s_cnt[0]);  // 0/0 = NaN, as torch
     *loss = total;
     if (n_valid != nullptr) *n_valid = static_cast<int64_t>(s_cnt[0]);
+    if (n_correct != nullptr) *n_correct = static_cast<int64_t>(s_cor[0]);
+    if (entropy_sum != nullptr) *entropy_sum = static_cast<float>(s_ent[0]);
+  }
+}
+
+// =============================================================================================
+// Valid-row compaction: rows whose label is ignore_index add nothing to the loss, to dW, and get
+// a zero dX row, so the three kernels below let every GEMM run on the live rows only.  The live
+// count stays on the device (GemmShape::dyn_rows); nothing here synchronises the host.
+// =============================================================================================
+
+// One block.  Stable compaction of the non-ignored rows:
+//   row_index[j] = original row of compact row j (j < n_live)      labels_c[j] = its label
+//   pos[r]       = compact position of original row r, or -1        *n_live    = live count
+__global__ void compact_labels_kernel(const int32_t* __restrict__ labels, int N, int ignore_index,
+                                      int32_t* __restrict__ row_index, int32_t* __restrict__ labels_c,
+                                      int32_t* __restrict__ pos, int* __restrict__ n_live) {
+  __shared__ int s_off[1024];
+  const int per = (N + blockDim.x - 1) / blockDim.x;
+  const int lo = min(static_cast<int>(threadIdx.x) * per, N), hi = min(lo + per, N);
+  int cnt = 0;
+  for (int i = lo; i < hi; ++i) cnt += (labels[i] != ignore_index) ? 1 : 0;
+  s_off[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int off = 1; off < static_cast<int>(blockDim.x); off <<= 1) {  // inclusive Hillis-Steele scan
+    int v = (static_cast<int>(threadIdx.x) >= off) ? s_off[threadIdx.x - off] : 0;
+    __syncthreads();
+    s_off[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int at = s_off[threadIdx.x] - cnt;
+  for (int i = lo; i < hi; ++i) {
+    const int l = labels[i];
+    if (l != ignore_index) {
+      row_index[at] = i;
+      labels_c[at] = l;
+      pos[i] = at;
+      ++at;
+    } else {
+      pos[i] = -1;
+    }
+  }
+  const int total = s_off[blockDim.x - 1];
+  for (int j = total + static_cast<int>(threadIdx.x); j < N; j += blockDim.x) labels_c[j] = ignore_index;  // dead tail
+  if (threadIdx.x == 0) *n_live = total;
+}
+
+// xc[j,:] = x[row_index[j],:] for j < n_live; rows up to the next multiple of 128 are zero-filled
+// (GEMMs that contract over rows consume whole 64-row blocks).  One warp per row, 16-byte accesses.
+__global__ void gather_rows_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ row_index,
+                                   const int* __restrict__ n_live, int N, int H, __nv_bfloat16* __restrict__ xc) {
+  const int live = min(max(*n_live, 0), N);
+  const int padded = min((live + 127) / 128 * 128, N);
+  const int warps_per_block = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const int vec = H / 8;
+  for (int j = blockIdx.x * warps_per_block + (threadIdx.x >> 5); j < padded; j += gridDim.x * warps_per_block) {
+    uint4* dst = reinterpret_cast<uint4*>(xc + static_cast<size_t>(j) * H);
+    if (j < live) {
+      const uint4* src = reinterpret_cast<const uint4*>(x + static_cast<size_t>(row_index[j]) * H);
+      for (int v = lane; v < vec; v += 32) dst[v] = src[v];
+    } else {
+      for (int v = lane; v < vec; v += 32) dst[v] = make_uint4(0, 0, 0, 0);
+    }
+  }
+}
+
+// dx[r,:] = dxc[pos[r],:] if pos[r] >= 0 else 0 -- every output row is written exactly once.
+__global__ void scatter_rows_kernel(const __nv_bfloat16* __restrict__ dxc, const int32_t* __restrict__ pos, int N, int H,
+                                    __nv_bfloat16* __restrict__ dx) {
+  const int warps_per_block = blockDim.x >> 5, lane = threadIdx.x & 31;
+  const int vec = H / 8;
+  for (int r = blockIdx.x * warps_per_block + (threadIdx.x >> 5); r < N; r += gridDim.x * warps_per_block) {
+    uint4* dst = reinterpret_cast<uint4*>(dx + static_cast<size_t>(r) * H);
+    const int j = pos[r];
+    if (j >= 0) {
+      const uint4* src = reinterpret_cast<const uint4*>(dxc + static_cast<size_t>(j) * H);
+      for (int v = lane; v < vec; v += 32) dst[v] = src[v];
+    } else {
+      for (int v = lane; v < vec; v += 32) dst[v] = make_uint4(0, 0, 0, 0);
+    }
   }
 }
 
@@ -365,7 +496,7 @@ constexpr int GROUP_M_TILES = 64;
 
 template <class Epi, bool A_MN, bool B_MN>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
-                const typename Epi::Params& ep, cudaStream_t stream) {
+                const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
   CUtensorMap ta, tb;
   int rc = make_operand_tmap(&ta, a, M, K, lda, A_MN, BLOCK_M);
@@ -380,6 +511,8 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
   s.m_fastest = m_fastest;
   s.group_m = s.tiles_m < GROUP_M_TILES ? s.tiles_m : GROUP_M_TILES;
+  s.dyn_rows = dyn_rows;
+  s.dyn_is_k = dyn_is_k;
   auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
   B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
@@ -422,6 +555,96 @@ int check_dims(int N, int H, int V) {
 
 using namespace b200;
 
+namespace {
+
+struct FwdScratch {
+  float2* partials;
+  float* partials_ez;
+  float* tgt;
+  float* row_loss;
+  float* row_entropy;
+  unsigned char* row_correct;
+};
+
+size_t fwd_workspace_bytes(int N, int V, bool stats) {
+  if (N <= 0 || V <= 0) return 0;
+  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
+  size_t b = align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);  // partials
+  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // target logits
+  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // row losses
+  if (stats) {
+    b += align_up(tiles_n * static_cast<size_t>(N) * sizeof(float), 256);  // sum exp*z partials
+    b += align_up(static_cast<size_t>(N) * sizeof(float), 256);            // row entropies
+    b += align_up(static_cast<size_t>(N), 256);                            // row correct flags
+  }
+  return b;
+}
+
+FwdScratch carve_fwd(void* workspace, int N, int V, bool stats) {
+  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  FwdScratch f = {};
+  f.partials = reinterpret_cast<float2*>(ws);
+  ws += align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);
+  f.tgt = reinterpret_cast<float*>(ws);
+  ws += align_up(static_cast<size_t>(N) * sizeof(float), 256);
+  f.row_loss = reinterpret_cast<float*>(ws);
+  ws += align_up(static_cast<size_t>(N) * sizeof(float), 256);
+  if (stats) {
+    f.partials_ez = reinterpret_cast<float*>(ws);
+    ws += align_up(tiles_n * static_cast<size_t>(N) * sizeof(float), 256);
+    f.row_entropy = reinterpret_cast<float*>(ws);
+    ws += align_up(static_cast<size_t>(N) * sizeof(float), 256);
+    f.row_correct = ws;
+  }
+  return f;
+}
+
+// Shared body of the forward entry points.  `n_rows_dev` (nullable) = live rows on the device.
+int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, int H, int V, int ignore_index,
+                  float scale, int denom_mode, const int64_t* denom, uint32_t flags, const int32_t* n_rows_dev,
+                  float* loss, float* lse, int64_t* n_valid, bool stats, int64_t* n_correct, float* entropy_sum,
+                  void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  int rc = check_dims(N, H, V);
+  if (rc != 0) return rc;
+  if (!x || !w || !labels || !loss || !lse) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (stats && (!n_correct || !entropy_sum)) return fail(B200SFT_ERR_INVALID, "null statistics pointer");
+  if (denom_mode == B200SFT_DENOM_DEVICE && denom == nullptr)
+    return fail(B200SFT_ERR_INVALID, "denom_mode DEVICE needs a denom pointer");
+  if (denom_mode < 0 || denom_mode > 2) return fail(B200SFT_ERR_INVALID, "bad denom_mode %d", denom_mode);
+  const size_t need = fwd_workspace_bytes(N, V, stats);
+  if (workspace == nullptr || workspace_bytes < need)
+    return fail(B200SFT_ERR_WORKSPACE, "flce_fwd workspace too small: have %zu, need %zu", workspace_bytes, need);
+  const FwdScratch f = carve_fwd(workspace, N, V, stats);
+  const int tiles_n = (V + BLOCK_N - 1) / BLOCK_N;
+
+  // Rows whose label is ignored (or, defensively, outside [0,V)) never get a target logit written.
+  B200_CUDA_CHECK(cudaMemsetAsync(f.tgt, 0, static_cast<size_t>(N) * sizeof(float), stream));
+
+  if (stats) {
+    FwdSoftmaxEpi<true>::Params ep = {labels, f.partials, f.partials_ez, f.tgt, N,
+                                      (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0};
+    rc = launch_gemm<FwdSoftmaxEpi<true>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream, n_rows_dev, 0);
+  } else {
+    FwdSoftmaxEpi<false>::Params ep = {labels, f.partials, nullptr, f.tgt, N,
+                                       (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0};
+    rc = launch_gemm<FwdSoftmaxEpi<false>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream, n_rows_dev, 0);
+  }
+  if (rc != 0) return rc;
+
+  flce_merge_rows_kernel<<<(N + 255) / 256, 256, 0, stream>>>(f.partials, f.partials_ez, f.tgt, labels, N, n_rows_dev,
+                                                               tiles_n, ignore_index, lse, f.row_loss, f.row_entropy,
+                                                               f.row_correct);
+  B200_CUDA_CHECK(cudaGetLastError());
+  flce_reduce_loss_kernel<<<1, 1024, 0, stream>>>(f.row_loss, f.row_entropy, f.row_correct, labels, N, n_rows_dev,
+                                                  ignore_index, scale, denom_mode, denom, loss, n_valid, n_correct,
+                                                  entropy_sum);
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+}  // namespace
+
 // =============================================================================================
 // C ABI
 // =============================================================================================
@@ -429,52 +652,56 @@ extern "C" {
 
 size_t b200sft_flce_fwd_workspace_bytes(int N, int H, int V) {
   (void)H;
-  if (N <= 0 || V <= 0) return 0;
-  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
-  size_t b = align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);  // partials
-  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // target logits
-  b += align_up(static_cast<size_t>(N) * sizeof(float), 256);                   // row losses
-  return b;
+  return fwd_workspace_bytes(N, V, false);
+}
+
+size_t b200sft_flce_fwd_stats_workspace_bytes(int N, int H, int V) {
+  (void)H;
+  return fwd_workspace_bytes(N, V, true);
 }
 
 int b200sft_flce_fwd(const void* x, const void* w, const int32_t* labels, int N, int H, int V, int ignore_index,
-                     float scale, int denom_mode, const int64_t* denom, uint32_t flags, float* loss, float* lse,
-                     int64_t* n_valid, void* workspace, size_t workspace_bytes, void* stream_) {
+                     float scale, int denom_mode, const int64_t* denom, uint32_t flags, const int32_t* n_rows_dev,
+                     float* loss, float* lse, int64_t* n_valid, void* workspace, size_t workspace_bytes, void* stream) {
+  return flce_fwd_impl(x, w, labels, N, H, V, ignore_index, scale, denom_mode, denom, flags, n_rows_dev, loss, lse,
+                       n_valid, false, nullptr, nullptr, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int b200sft_flce_fwd_stats(const void* x, const void* w, const int32_t* labels, int N, int H, int V, int ignore_index,
+                           float scale, int denom_mode, const int64_t* denom, uint32_t flags,
+                           const int32_t* n_rows_dev, float* loss, float* lse, int64_t* n_valid, int64_t* n_correct,
+                           float* entropy_sum, void* workspace, size_t workspace_bytes, void* stream) {
+  return flce_fwd_impl(x, w, labels, N, H, V, ignore_index, scale, denom_mode, denom, flags, n_rows_dev, loss, lse,
+                       n_valid, true, n_correct, entropy_sum, workspace, workspace_bytes,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int ignore_index, void* xc,
+                         int32_t* labels_c, int32_t* row_index, int32_t* pos, int32_t* n_live, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  int rc = check_dims(N, H, V);
-  if (rc != 0) return rc;
-  if (!x || !w || !labels || !loss || !lse) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
-  if (denom_mode == B200SFT_DENOM_DEVICE && denom == nullptr)
-    return fail(B200SFT_ERR_INVALID, "denom_mode DEVICE needs a denom pointer");
-  if (denom_mode < 0 || denom_mode > 2) return fail(B200SFT_ERR_INVALID, "bad denom_mode %d", denom_mode);
-  const size_t need = b200sft_flce_fwd_workspace_bytes(N, H, V);
-  if (workspace == nullptr || workspace_bytes < need)
-    return fail(B200SFT_ERR_WORKSPACE, "flce_fwd workspace too small: have %zu, need %zu", workspace_bytes, need);
-
-  const size_t tiles_n = (static_cast<size_t>(V) + BLOCK_N - 1) / BLOCK_N;
-  uint8_t* ws = static_cast<uint8_t*>(workspace);
-  float2* partials = reinterpret_cast<float2*>(ws);
-  ws += align_up(tiles_n * static_cast<size_t>(N) * sizeof(float2), 256);
-  float* tgt = reinterpret_cast<float*>(ws);
-  ws += align_up(static_cast<size_t>(N) * sizeof(float), 256);
-  float* row_loss = reinterpret_cast<float*>(ws);
-
-  // Rows whose label is ignored (or, defensively, outside [0,V)) never get a target logit written.
-  B200_CUDA_CHECK(cudaMemsetAsync(tgt, 0, static_cast<size_t>(N) * sizeof(float), stream));
-
-  FwdSoftmaxEpi::Params ep;
-  ep.labels = labels;
-  ep.partials = partials;
-  ep.tgt_logit = tgt;
-  ep.round_bf16 = (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0;
-  rc = launch_gemm<FwdSoftmaxEpi, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream);
-  if (rc != 0) return rc;
-
-  flce_merge_rows_kernel<<<(N + 255) / 256, 256, 0, stream>>>(partials, tgt, labels, N, static_cast<int>(tiles_n),
-                                                               ignore_index, lse, row_loss);
+  if (N <= 0 || H <= 0 || H % 8 != 0) return fail(B200SFT_ERR_INVALID, "compact_rows: bad shape N=%d H=%d", N, H);
+  if (!x || !labels || !xc || !labels_c || !row_index || !pos || !n_live)
+    return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  compact_labels_kernel<<<1, 1024, 0, stream>>>(labels, N, ignore_index, row_index, labels_c, pos, n_live);
   B200_CUDA_CHECK(cudaGetLastError());
-  flce_reduce_loss_kernel<<<1, 1024, 0, stream>>>(row_loss, labels, N, ignore_index, scale, denom_mode, denom, loss,
-                                                  n_valid);
+  const int warps = 8;
+  int grid = (N + warps - 1) / warps;
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  gather_rows_kernel<<<grid, warps * 32, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), row_index, n_live, N, H,
+                                                       static_cast<__nv_bfloat16*>(xc));
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_scatter_rows(const void* dxc, const int32_t* pos, int N, int H, void* dx, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (N <= 0 || H <= 0 || H % 8 != 0) return fail(B200SFT_ERR_INVALID, "scatter_rows: bad shape N=%d H=%d", N, H);
+  if (!dxc || !pos || !dx) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  const int warps = 8;
+  int grid = (N + warps - 1) / warps;
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  scatter_rows_kernel<<<grid, warps * 32, 0, stream>>>(static_cast<const __nv_bfloat16*>(dxc), pos, N, H,
+                                                        static_cast<__nv_bfloat16*>(dx));
   B200_CUDA_CHECK(cudaGetLastError());
   return B200SFT_OK;
 }
@@ -489,8 +716,8 @@ size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols) {
 
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse, const float* grad_out,
                      int N, int H, int V, int ignore_index, float scale, int denom_mode, const int64_t* denom,
-                     uint32_t flags, int chunk_cols, void* dx, void* dw, void* workspace, size_t workspace_bytes,
-                     void* stream_) {
+                     uint32_t flags, int chunk_cols, const int32_t* n_rows_dev, void* dx, void* dw, void* workspace,
+                     size_t workspace_bytes, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   int rc = check_dims(N, H, V);
   if (rc != 0) return rc;
@@ -532,7 +759,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     dp.out = dlog;
     dp.ld = slab;
     dp.col_offset = v0;
-    rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream);
+    dp.rows_alloc = N;
+    rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream, n_rows_dev, 0);
     if (rc != 0) return rc;
 
     // (2) dX[N,H] (+)= dlogits[N,cols] . W[v0:v0+cols, :]     A K-major, B = W rows read MN-major
@@ -548,7 +776,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
       sx.mode = ACCUM_F32_OUT_BF16;
     else
       sx.mode = ACCUM_F32;
-    rc = launch_gemm<StoreEpi, false, true>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream);
+    rc = launch_gemm<StoreEpi, false, true>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream, n_rows_dev, 0);
     if (rc != 0) return rc;
 
     // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every
@@ -558,7 +786,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     sw.acc = nullptr;
     sw.ld = H;
     sw.mode = STORE_BF16;
-    rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream);
+    rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, n_rows_dev, 1);
     if (rc != 0) return rc;
   }
   return B200SFT_OK;
@@ -631,6 +859,6 @@ extern "C" int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int3
   // per-tile partials and row losses are fully rewritten for this call's N and V, and the
   // target-logit slots (the one region that must start at zero) are cleared in-stream by the
   // forward path itself before the GEMM.
-  return b200sft_flce_fwd(x, w, labels, N, H, V, ignore_index, scale, denom_mode, denom, flags, loss, lse, n_valid,
-                          scratch, static_cast<size_t>(B200SFT_NOALLOC_SCRATCH_BYTES), stream);
+  return b200sft_flce_fwd(x, w, labels, N, H, V, ignore_index, scale, denom_mode, denom, flags, /*n_rows_dev=*/nullptr,
+                          loss, lse, n_valid, scratch, static_cast<size_t>(B200SFT_NOALLOC_SCRATCH_BYTES), stream);
 }

@@ -37,6 +37,11 @@ struct GemmShape {
   int m_fastest;  // tile order: 1 = consecutive CTAs walk M for a fixed N tile (shares the B panel in L2)
   int group_m;    // m_fastest only: M tiles per rasterisation group.  All N tiles of a group are finished
                   // before the next group starts, so the group's A rows stay resident in L2.
+  // Optional live row count on the device (valid-row compaction: the host never learns it).  When
+  // non-null it replaces M (dyn_is_k = 0) or K (dyn_is_k = 1); the static value is the capacity the
+  // tensor maps were built for.
+  const int* dyn_rows;
+  int dyn_is_k;
 };
 
 struct TileCoord {
@@ -73,7 +78,18 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
 template <class Epi, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                        const GemmShape shape, const typename Epi::Params epi_params) {
+                        const GemmShape shape_in, const typename Epi::Params epi_params) {
+  GemmShape shape = shape_in;
+  if (shape.dyn_rows != nullptr) {
+    int r = __ldg(shape.dyn_rows);
+    if (shape.dyn_is_k) {
+      shape.K = r < shape.K ? (r < 0 ? 0 : r) : shape.K;
+    } else {
+      shape.M = r < shape.M ? (r < 0 ? 0 : r) : shape.M;
+      shape.tiles_m = (shape.M + BLOCK_M - 1) / BLOCK_M;
+      if (shape.group_m > shape.tiles_m) shape.group_m = shape.tiles_m > 0 ? shape.tiles_m : 1;
+    }
+  }
   extern __shared__ uint8_t smem_raw[];
   // 128B-swizzled tiles must be 1024-byte aligned (descriptor base_offset = 0).
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -202,8 +218,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       for (int c = 0; c < BLOCK_N; c += 32) {
         uint32_t acc[32];
         __syncwarp();  // epilogue functors may diverge per row; tcgen05.ld is warp-collective
-        tmem_ld_32x32b_x32(taddr + c, acc);
-        tmem_ld_wait();
+        if (num_kb > 0) {
+          tmem_ld_32x32b_x32(taddr + c, acc);
+          tmem_ld_wait();
+        } else {  // empty contraction (no live rows): the accumulator was never written
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[j] = 0u;
+        }
         epi.chunk(tc, row_in_tile, c, acc);
       }
       tc_fence_before_sync();

@@ -46,6 +46,7 @@ class FusedLMHead(nn.Module):
         self.out_features = linear.out_features
         self.weight = linear.weight
         self.armed = False
+        self.last_stats = None  # {"n_valid", "n_correct", "entropy_sum"} of the latest fused call (token_stats)
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         if self.armed:
@@ -62,8 +63,13 @@ def _unwrap(model: nn.Module) -> nn.Module:
     return model
 
 
-def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0) -> nn.Module:
-    """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model."""
+def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
+                       token_stats: bool = False) -> nn.Module:
+    """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model.
+
+    ``skip_ignored_rows``: compact away positions labelled -100 (padding, prompt, packed-sample
+    boundaries) before the GEMMs.  ``token_stats``: also produce the logits-free token-accuracy
+    count and entropy sum; the latest values are kept in ``model.lm_head.last_stats``."""
     inner = _unwrap(model)
     head = getattr(inner, "lm_head", None)
     if head is None:
@@ -75,7 +81,11 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0) ->
 
     def loss_function(logits, labels, vocab_size=None, **kwargs):
         if head.armed:
-            return fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_cols=chunk_cols, **kwargs)
+            out = fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_cols=chunk_cols,
+                                       skip_ignored_rows=skip_ignored_rows, return_stats=token_stats, **kwargs)
+            if token_stats:
+                out, head.last_stats = out
+            return out
         return stock_loss(logits=logits, labels=labels, vocab_size=vocab_size, **kwargs)
 
     if not getattr(inner, "_b200sft_patched", False):
@@ -101,7 +111,8 @@ def fused_head_armed(model: nn.Module):
 def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                          num_items_in_batch: Optional[Union[torch.Tensor, int]] = None,
                          ignore_index: int = -100, shift_labels: Optional[torch.Tensor] = None,
-                         flags: int = 0, chunk_cols: int = 0, **_unused: Any) -> torch.Tensor:
+                         flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
+                         return_stats: bool = False, **_unused: Any):
     """``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:45-67) on hidden states.
 
     Same arguments and meaning, except that the first argument holds ``[B,T,H]`` hidden states:
@@ -121,7 +132,8 @@ def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labe
         h2 = h2.to(torch.bfloat16)
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     return ops.fused_linear_cross_entropy(h2.contiguous(), w.contiguous(), shifted, num_items_in_batch,
-                                          ignore_index=ignore_index, flags=flags, chunk_cols=chunk_cols)
+                                          ignore_index=ignore_index, flags=flags, chunk_cols=chunk_cols,
+                                          skip_ignored_rows=skip_ignored_rows, return_stats=return_stats)
 
 
 class FusedCELossMixin:
@@ -140,12 +152,15 @@ class FusedCELossMixin:
 
     b200sft_flags: int = 0
     b200sft_chunk_cols: int = 0
+    b200sft_skip_ignored_rows: bool = True
+    b200sft_token_stats: bool = False  # True: log mean_token_accuracy / entropy like TRL, without logits
     b200sft_register_comm_hook: bool = True
 
     def _b200sft_prepare(self, model: nn.Module) -> None:
         inner = _unwrap(model)
         if not isinstance(getattr(inner, "lm_head", None), FusedLMHead):
-            install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_cols)
+            install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_cols, self.b200sft_skip_ignored_rows,
+                               self.b200sft_token_stats)
         if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)
                 and not getattr(model, "_b200sft_hook", False)):
             from .comm_hook import register_b200_comm_hook
@@ -178,6 +193,13 @@ class FusedCELossMixin:
                 f"{','.join(outputs.keys())}. For reference, the inputs it received are {','.join(inputs.keys())}."
             )
         loss = outputs["loss"] if isinstance(outputs, dict) else outputs[0]
+        stats = _unwrap(model).lm_head.last_stats
+        if self.b200sft_token_stats and stats is not None and hasattr(self, "_metrics"):
+            # [TRL, not on disk] SFTTrainer keeps per-mode lists in self._metrics and averages them at log time
+            mode = "train" if model.training else "eval"
+            nv = stats["n_valid"].clamp(min=1).float()
+            self._metrics[mode]["mean_token_accuracy"].append((stats["n_correct"].float() / nv).item())
+            self._metrics[mode]["entropy"].append((stats["entropy_sum"] / nv).item())
         args = getattr(self, "args", None)
         average = getattr(args, "average_tokens_across_devices", True)
         if average and num_items_in_batch is not None and getattr(self, "model_accepts_loss_kwargs", True):

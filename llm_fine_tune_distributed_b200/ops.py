@@ -62,8 +62,9 @@ def _bwd_num_slabs(N: int, V: int, chunk_cols: int) -> int:
 
 
 __all__ = [
-    "label_prep", "flce_forward", "flce_backward", "gemm_bf16", "scale_", "scale_cast_f32_to_bf16",
-    "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX", "FLAG_ROUND_LOGITS_BF16",
+    "label_prep", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
+    "scale_cast_f32_to_bf16", "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX",
+    "FLAG_ROUND_LOGITS_BF16",
 ]
 
 
@@ -126,12 +127,15 @@ def _check_flce_inputs(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -
 
 def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: float = 1.0,
                  denom: Optional[torch.Tensor] = None, reduction_mean: bool = False,
-                 ignore_index: int = IGNORE_INDEX, flags: int = 0
-                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """loss, lse, n_valid = fused lm_head + cross-entropy forward; no [N,V] tensor is allocated.
+                 ignore_index: int = IGNORE_INDEX, flags: int = 0, n_rows: Optional[torch.Tensor] = None,
+                 with_stats: bool = False):
+    """loss, lse, n_valid[, n_correct, entropy_sum] = fused lm_head + cross-entropy forward; no
+    [N,V] tensor is allocated.
 
     ``loss = scale * sum_valid(lse - z_target) / D`` with D = 1, ``*denom`` (int64 device scalar,
     the trainer's num_items_in_batch) or the local valid-row count (``reduction_mean``).
+    ``n_rows`` (int32 device scalar) = live rows when ``x``/``labels`` come from :func:`compact_rows`.
+    ``with_stats`` adds the logits-free token-accuracy count and entropy sum.
     """
     N, H, V = _check_flce_inputs(x, w, labels)
     if denom is not None and reduction_mean:
@@ -140,28 +144,45 @@ def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: 
         _require_cuda(denom)
         if denom.dtype != torch.int64 or denom.numel() != 1:
             raise ValueError("denom must be a single int64 on the device")
+    if n_rows is not None:
+        _require_cuda(n_rows)
+        if n_rows.dtype != torch.int32 or n_rows.numel() != 1:
+            raise ValueError("n_rows must be a single int32 on the device")
     mode = DENOM_DEVICE if denom is not None else (DENOM_VALID if reduction_mean else DENOM_NONE)
     lib = _cabi.load()
     with torch.cuda.device(x.device):
-        ws_bytes = lib.b200sft_flce_fwd_workspace_bytes(N, H, V)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
         loss = torch.empty((), dtype=torch.float32, device=x.device)
         lse = torch.empty(N, dtype=torch.float32, device=x.device)
         n_valid = torch.empty((), dtype=torch.int64, device=x.device)
         ev = STATS.begin("flce_fwd", x.device)
-        check(lib.b200sft_flce_fwd(_ptr(x), _ptr(w), _ptr(labels), N, H, V, ignore_index, float(scale), mode,
-                                   _ptr(denom), flags, _ptr(loss), _ptr(lse), _ptr(n_valid), _ptr(ws), ws_bytes,
-                                   _stream_ptr(x)), "b200sft_flce_fwd")
+        if with_stats:
+            ws_bytes = lib.b200sft_flce_fwd_stats_workspace_bytes(N, H, V)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+            n_correct = torch.empty((), dtype=torch.int64, device=x.device)
+            entropy_sum = torch.empty((), dtype=torch.float32, device=x.device)
+            check(lib.b200sft_flce_fwd_stats(_ptr(x), _ptr(w), _ptr(labels), N, H, V, ignore_index, float(scale), mode,
+                                             _ptr(denom), flags, _ptr(n_rows), _ptr(loss), _ptr(lse), _ptr(n_valid),
+                                             _ptr(n_correct), _ptr(entropy_sum), _ptr(ws), ws_bytes, _stream_ptr(x)),
+                  "b200sft_flce_fwd_stats")
+        else:
+            ws_bytes = lib.b200sft_flce_fwd_workspace_bytes(N, H, V)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+            check(lib.b200sft_flce_fwd(_ptr(x), _ptr(w), _ptr(labels), N, H, V, ignore_index, float(scale), mode,
+                                       _ptr(denom), flags, _ptr(n_rows), _ptr(loss), _ptr(lse), _ptr(n_valid),
+                                       _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_fwd")
         STATS.end(ev, x.device)
         STATS.kernel_launches += 3  # GEMM+softmax epilogue, row merge, loss reduce
+    if with_stats:
+        return loss, lse, n_valid, n_correct, entropy_sum
     return loss, lse, n_valid
 
 
 def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                   grad_out: torch.Tensor, scale: float = 1.0, denom: Optional[torch.Tensor] = None,
-                  ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0
-                  ) -> Tuple[torch.Tensor, torch.Tensor]:
-    """dx [N,H] bf16, dw [V,H] bf16 for the loss produced by :func:`flce_forward`."""
+                  ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0,
+                  n_rows: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """dx [N,H] bf16, dw [V,H] bf16 for the loss produced by :func:`flce_forward` (with compacted
+    inputs and ``n_rows``, dx is compact too: expand it with :func:`scatter_rows`)."""
     N, H, V = _check_flce_inputs(x, w, labels)
     _require_cuda(lse, grad_out)
     if lse.dtype != torch.float32 or lse.shape != (N,):
@@ -176,11 +197,46 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
         dw = torch.empty_like(w)
         ev = STATS.begin("flce_bwd", x.device)
         check(lib.b200sft_flce_bwd(_ptr(x), _ptr(w), _ptr(labels), _ptr(lse), _ptr(grad_out), N, H, V,
-                                   ignore_index, float(scale), mode, _ptr(denom), flags, chunk_cols, _ptr(dx),
-                                   _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
+                                   ignore_index, float(scale), mode, _ptr(denom), flags, chunk_cols, _ptr(n_rows),
+                                   _ptr(dx), _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
         STATS.end(ev, x.device)
         STATS.kernel_launches += 3 * _bwd_num_slabs(N, V, chunk_cols)  # dlogits, dX, dW GEMMs per vocabulary slab
     return dx, dw
+
+
+def compact_rows(x: torch.Tensor, labels: torch.Tensor, ignore_index: int = IGNORE_INDEX):
+    """Gather the rows whose label is not ``ignore_index`` (stable order).  Returns
+    ``(xc [N,H], labels_c [N], row_index [N], pos [N], n_live int32 scalar)`` -- all on the device;
+    the live count is never read by the host."""
+    _require_cuda(x, labels)
+    if x.dtype != torch.bfloat16 or labels.dtype != torch.int32 or x.dim() != 2 or labels.shape != (x.shape[0],):
+        raise ValueError("x must be bf16 [N,H] and labels int32 [N]")
+    if not (x.is_contiguous() and labels.is_contiguous()):
+        raise ValueError("x and labels must be contiguous")
+    N, H = x.shape
+    lib = _cabi.load()
+    with torch.cuda.device(x.device):
+        xc = torch.empty_like(x)
+        labels_c = torch.empty_like(labels)
+        row_index = torch.empty_like(labels)
+        pos = torch.empty_like(labels)
+        n_live = torch.empty((), dtype=torch.int32, device=x.device)
+        check(lib.b200sft_compact_rows(_ptr(x), _ptr(labels), N, H, ignore_index, _ptr(xc), _ptr(labels_c),
+                                       _ptr(row_index), _ptr(pos), _ptr(n_live), _stream_ptr(x)), "b200sft_compact_rows")
+        STATS.kernel_launches += 2
+    return xc, labels_c, row_index, pos, n_live
+
+
+def scatter_rows(dxc: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
+    """dx[r] = dxc[pos[r]] if pos[r] >= 0 else 0 (inverse of :func:`compact_rows` for gradients)."""
+    _require_cuda(dxc, pos)
+    N, H = dxc.shape
+    lib = _cabi.load()
+    with torch.cuda.device(dxc.device):
+        dx = torch.empty_like(dxc)
+        check(lib.b200sft_scatter_rows(_ptr(dxc), _ptr(pos), N, H, _ptr(dx), _stream_ptr(dxc)), "b200sft_scatter_rows")
+        STATS.kernel_launches += 1
+    return dx
 
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, a_mn_major: bool = False,
@@ -258,65 +314,83 @@ def cast_bf16_to_f32(src: torch.Tensor, out: torch.Tensor, scale: float = 1.0) -
 # --------------------------------------------------------------------------------------------
 @torch.library.custom_op("b200sft::flce_fwd", mutates_args=())
 def _flce_fwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: float,
-                 denom: Optional[torch.Tensor], reduction_mean: bool, ignore_index: int,
-                 flags: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    return flce_forward(x, w, labels, scale, denom, reduction_mean, ignore_index, flags)
+                 denom: Optional[torch.Tensor], reduction_mean: bool, ignore_index: int, flags: int,
+                 n_rows: Optional[torch.Tensor], with_stats: bool
+                 ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    out = flce_forward(x, w, labels, scale, denom, reduction_mean, ignore_index, flags, n_rows, with_stats)
+    if with_stats:
+        return out
+    return (*out, x.new_zeros((), dtype=torch.int64), x.new_zeros((), dtype=torch.float32))
 
 
 @_flce_fwd_op.register_fake
-def _(x, w, labels, scale, denom, reduction_mean, ignore_index, flags):
+def _(x, w, labels, scale, denom, reduction_mean, ignore_index, flags, n_rows, with_stats):
     return (x.new_empty((), dtype=torch.float32), x.new_empty((x.shape[0],), dtype=torch.float32),
-            x.new_empty((), dtype=torch.int64))
+            x.new_empty((), dtype=torch.int64), x.new_empty((), dtype=torch.int64),
+            x.new_empty((), dtype=torch.float32))
 
 
 @torch.library.custom_op("b200sft::flce_bwd", mutates_args=())
 def _flce_bwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                  grad_out: torch.Tensor, scale: float, denom: Optional[torch.Tensor], ignore_index: int,
-                 flags: int, chunk_cols: int) -> Tuple[torch.Tensor, torch.Tensor]:
-    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols)
+                 flags: int, chunk_cols: int, n_rows: Optional[torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
+    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows)
 
 
 @_flce_bwd_op.register_fake
-def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols):
+def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows):
     return torch.empty_like(x), torch.empty_like(w)
 
 
 class _FusedLinearCrossEntropy(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_cols):
-        loss, lse, n_valid = torch.ops.b200sft.flce_fwd(x, w, labels, scale, denom, reduction_mean, ignore_index,
-                                                        flags)
+    def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_cols, skip_ignored,
+                with_stats):
+        pos = n_rows = None
+        xk, lk = x, labels
+        if skip_ignored:  # run every GEMM on the live rows only
+            xk, lk, _row_index, pos, n_rows = compact_rows(x, labels, ignore_index)
+        loss, lse, n_valid, n_correct, entropy_sum = torch.ops.b200sft.flce_fwd(
+            xk, w, lk, scale, denom, reduction_mean, ignore_index, flags, n_rows, with_stats)
         # reduction="mean" divides by the local valid count; backward takes it as a device scalar
         bwd_denom = n_valid if reduction_mean else denom
-        ctx.save_for_backward(x, w, labels, lse, bwd_denom)
+        ctx.save_for_backward(xk, w, lk, lse, bwd_denom, pos, n_rows)
         ctx.scale, ctx.ignore_index, ctx.flags, ctx.chunk_cols = scale, ignore_index, flags, chunk_cols
-        ctx.mark_non_differentiable(lse, n_valid)
-        return loss, lse, n_valid
+        ctx.mark_non_differentiable(n_valid, n_correct, entropy_sum)
+        return loss, n_valid, n_correct, entropy_sum
 
     @staticmethod
-    def backward(ctx, grad_loss, _g_lse, _g_nvalid):
-        x, w, labels, lse, bwd_denom = ctx.saved_tensors
-        dx, dw = torch.ops.b200sft.flce_bwd(x, w, labels, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
-                                            ctx.flags, ctx.chunk_cols)
-        return dx, dw, None, None, None, None, None, None, None
+    def backward(ctx, grad_loss, *_unused):
+        xk, w, lk, lse, bwd_denom, pos, n_rows = ctx.saved_tensors
+        dx, dw = torch.ops.b200sft.flce_bwd(xk, w, lk, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
+                                            ctx.flags, ctx.chunk_cols, n_rows)
+        if pos is not None:
+            dx = scatter_rows(dx, pos)
+        return dx, dw, None, None, None, None, None, None, None, None, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,
                                num_items_in_batch: Optional[torch.Tensor] = None, scale: float = 1.0,
-                               ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0
-                               ) -> torch.Tensor:
+                               ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0,
+                               skip_ignored_rows: bool = False, return_stats: bool = False):
     """Differentiable ``cross_entropy(hidden @ weight.T, shifted_labels)`` without the logits.
 
     ``num_items_in_batch`` None -> mean over local valid rows (``reduction="mean"``), else the
     sum divided by that device scalar -- SP/transformers/loss/loss_utils.py:28-42.
     ``hidden`` is [N,H] bf16, ``weight`` [V,H] bf16, ``shifted_labels`` int32 [N] from
-    :func:`label_prep`.
+    :func:`label_prep`.  ``skip_ignored_rows`` compacts away rows labelled ``ignore_index`` first
+    (same result; less work when many rows are masked).  ``return_stats`` -> ``(loss, stats)`` with
+    ``stats = {"n_valid", "n_correct", "entropy_sum"}`` device scalars (token accuracy and mean
+    entropy are n_correct / n_valid and entropy_sum / n_valid).
     """
     denom = None
     if num_items_in_batch is not None:
         if not torch.is_tensor(num_items_in_batch):
             num_items_in_batch = torch.tensor(int(num_items_in_batch), dtype=torch.int64, device=hidden.device)
         denom = num_items_in_batch.to(device=hidden.device, dtype=torch.int64).reshape(())
-    loss, _, _ = _FusedLinearCrossEntropy.apply(hidden, weight, shifted_labels, float(scale), denom,
-                                                num_items_in_batch is None, ignore_index, flags, chunk_cols)
+    loss, n_valid, n_correct, entropy_sum = _FusedLinearCrossEntropy.apply(
+        hidden, weight, shifted_labels, float(scale), denom, num_items_in_batch is None, ignore_index, flags,
+        chunk_cols, bool(skip_ignored_rows), bool(return_stats))
+    if return_stats:
+        return loss, {"n_valid": n_valid, "n_correct": n_correct, "entropy_sum": entropy_sum}
     return loss

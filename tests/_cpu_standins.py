@@ -13,9 +13,14 @@ def label_prep(labels, ignore_index=-100):
 
 
 def fused_linear_cross_entropy(hidden, weight, shifted_labels, num_items_in_batch=None, scale=1.0,
-                               ignore_index=-100, flags=0, chunk_cols=0):
+                               ignore_index=-100, flags=0, chunk_cols=0, skip_ignored_rows=False, return_stats=False):
     n = None if num_items_in_batch is None else float(num_items_in_batch)
-    return oracle.lm_head_ce(hidden, weight, shifted_labels.long(), n, ignore_index) * scale
+    loss = oracle.lm_head_ce(hidden, weight, shifted_labels.long(), n, ignore_index) * scale
+    if return_stats:
+        nc, ent = oracle.token_stats(hidden.detach(), weight.detach(), shifted_labels, ignore_index)
+        nv = int((shifted_labels != ignore_index).sum())
+        return loss, {"n_valid": torch.tensor(nv), "n_correct": torch.tensor(nc), "entropy_sum": torch.tensor(ent)}
+    return loss
 
 
 def install(monkeypatch_or_none=None):

@@ -51,9 +51,9 @@ def test_version_and_workspace_queries(lib):
 
 def test_argument_validation_without_launching(lib):
     # bad dims / null pointers are rejected before any CUDA call
-    rc = lib.b200sft_flce_fwd(None, None, None, 128, 2048, 128256, -100, 1.0, 0, None, 0, None, None, None, None, 0, None)
+    rc = lib.b200sft_flce_fwd(None, None, None, 128, 2048, 128256, -100, 1.0, 0, None, 0, None, None, None, None, None, 0, None)
     assert rc < 0 and b"null" in lib.b200sft_last_error()
-    rc = lib.b200sft_flce_fwd(None, None, None, 128, 2047, 128256, -100, 1.0, 0, None, 0, None, None, None, None, 0, None)
+    rc = lib.b200sft_flce_fwd(None, None, None, 128, 2047, 128256, -100, 1.0, 0, None, 0, None, None, None, None, None, 0, None)
     assert rc < 0 and b"multiples of 8" in lib.b200sft_last_error()
     rc = lib.b200sft_gemm_bf16(None, None, None, 1, 1, 1, 8, 8, 8, 0, 0, None)
     assert rc < 0

@@ -140,3 +140,94 @@ def test_flce_rejects_cpu_tensors():
     with pytest.raises(B200SftError):
         ops.flce_forward(torch.zeros(8, 8, dtype=torch.bfloat16), torch.zeros(8, 8, dtype=torch.bfloat16),
                          torch.zeros(8, dtype=torch.int32))
+
+
+@pytest.mark.parametrize("N,H,V,masked", [(512, 128, 2048, 0.0), (640, 256, 4096, 0.5), (1000, 72, 1000, 0.9),
+                                          (384, 64, 512, 0.997)])
+def test_flce_skip_ignored_rows_matches_dense_path_and_oracle(cuda_device, N, H, V, masked):
+    """Valid-row compaction (the live count never leaves the device) must not change the result."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = _case(N, H, V, masked, seed=7 * N + V, device=cuda_device)
+    lab = labels.to(torch.int32)
+    n_valid = int((labels != -100).sum())
+    denom = torch.tensor(max(n_valid, 1), dtype=torch.int64, device=cuda_device)
+    outs = []
+    for skip in (False, True):
+        xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        loss = ops.fused_linear_cross_entropy(xg, wg, lab, denom, skip_ignored_rows=skip)
+        loss.backward()
+        outs.append((loss.detach(), xg.grad, wg.grad))
+    torch.cuda.synchronize()
+    (l0, dx0, dw0), (l1, dx1, dw1) = outs
+    assert abs(l0.item() - l1.item()) <= 1e-5 * max(abs(l0.item()), 1e-6)
+    assert torch.equal(dx0, dx1)                        # each dX row depends on its own row only
+    assert torch.count_nonzero(dx1[labels == -100]) == 0
+    assert torch.allclose(dw0.float(), dw1.float(), rtol=2.0 ** -7, atol=1e-6)   # same sum, other order over rows
+    ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, float(denom))
+    assert abs(l1.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item()) + 1e-7
+    if n_valid > 0:
+        assert _cos(dx1, ref_dx) >= 0.999 and _cos(dw1, ref_dw) >= 0.999
+
+
+def test_flce_skip_ignored_rows_all_masked(cuda_device):
+    from llm_fine_tune_distributed_b200 import ops
+
+    N, H, V = 256, 64, 512
+    x, w, _ = _case(N, H, V, 0.0, seed=5, device=cuda_device)
+    lab = torch.full((N,), -100, dtype=torch.int32, device=cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    loss = ops.fused_linear_cross_entropy(xg, wg, lab, torch.tensor(3, dtype=torch.int64, device=cuda_device),
+                                          skip_ignored_rows=True)
+    loss.backward()
+    assert loss.item() == 0.0
+    assert torch.count_nonzero(xg.grad) == 0 and torch.count_nonzero(wg.grad) == 0
+
+
+@pytest.mark.parametrize("N,masked", [(1, 0.0), (130, 0.3), (8192, 0.6), (5000, 1.0)])
+def test_compact_and_scatter_rows_bit_exact(cuda_device, N, masked):
+    from llm_fine_tune_distributed_b200 import ops
+
+    H = 64
+    g = torch.Generator().manual_seed(N)
+    x = torch.randn(N, H, generator=g).to(torch.bfloat16).to(cuda_device)
+    labels = torch.randint(0, 1000, (N,), generator=g, dtype=torch.int32)
+    labels[torch.rand(N, generator=g) < masked] = -100
+    xc, labels_c, row_index, pos, n_live = ops.compact_rows(x, labels.to(cuda_device))
+    live, ref_pos, n = oracle.compact_rows_numpy(labels.numpy())
+    assert int(n_live) == n
+    assert np.array_equal(row_index.cpu().numpy()[:n], live)
+    assert np.array_equal(pos.cpu().numpy(), ref_pos)
+    assert np.array_equal(labels_c.cpu().numpy()[:n], labels.numpy()[live])
+    assert bool((labels_c[n:] == -100).all())
+    assert torch.equal(xc[:n].cpu(), x.cpu()[torch.from_numpy(live)])
+    pad = min((n + 127) // 128 * 128, N)
+    assert torch.count_nonzero(xc[n:pad]) == 0
+    back = ops.scatter_rows(xc, pos)
+    expect = x.clone()
+    expect[labels.to(cuda_device) == -100] = 0
+    assert torch.equal(back, expect)
+
+
+@pytest.mark.parametrize("N,H,V,masked,skip", [(256, 128, 1024, 0.0, False), (512, 64, 1000, 0.5, True),
+                                               (384, 256, 4096, 0.8, True)])
+def test_flce_token_stats_vs_oracle(cuda_device, N, H, V, masked, skip):
+    """Logits-free token accuracy / entropy vs the same metrics on materialised logits."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = _case(N, H, V, masked, seed=N + 3 * V, device=cuda_device)
+    x = x * 4  # sharpen the distribution so that some argmaxes hit their label
+    top = torch.nn.functional.linear(x, w).float().argmax(-1)
+    pick = torch.rand(N, generator=torch.Generator().manual_seed(1)).to(cuda_device) < 0.3
+    labels = torch.where(pick & (labels != -100), top, labels)   # make ~30 % of the valid rows "correct"
+    lab = labels.to(torch.int32)
+    # the reference's argmax sees bf16-rounded logits; emulate that rounding so "is the maximum" means the same
+    loss, stats = ops.fused_linear_cross_entropy(x, w, lab, None, skip_ignored_rows=skip, return_stats=True,
+                                                 flags=ops.FLAG_ROUND_LOGITS_BF16)
+    n_correct, ent = oracle.token_stats(x, w, labels)
+    n_valid = int((labels != -100).sum())
+    assert int(stats["n_valid"]) == n_valid
+    assert abs(int(stats["n_correct"]) - n_correct) <= max(1, n_valid // 200)   # only exact ties may differ
+    assert abs(float(stats["entropy_sum"]) - ent) <= 1e-3 * abs(ent) + 1e-3
+    ref = oracle.lm_head_ce(x, w, labels, None)
+    assert abs(loss.item() - ref.item()) <= 1e-3 * abs(ref.item())

@@ -39,14 +39,14 @@ def _run(lib, noalloc, x, w, labels, denom):
     lse = torch.full((N,), float("nan"), dtype=torch.float32, device=dev)
     n_valid = torch.full((), -1, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev).cuda_stream
-    common = (x.data_ptr(), w.data_ptr(), labels.data_ptr(), N, H, V, -100, 1.0, 1, denom.data_ptr(), 0,
-              loss.data_ptr(), lse.data_ptr(), n_valid.data_ptr())
+    head = (x.data_ptr(), w.data_ptr(), labels.data_ptr(), N, H, V, -100, 1.0, 1, denom.data_ptr(), 0)
+    outs = (loss.data_ptr(), lse.data_ptr(), n_valid.data_ptr())
     if noalloc:
-        rc = lib.b200sft_flce_fwd_noalloc(*common, stream)
+        rc = lib.b200sft_flce_fwd_noalloc(*head, *outs, stream)
     else:
         ws_bytes = lib.b200sft_flce_fwd_workspace_bytes(N, H, V)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        rc = lib.b200sft_flce_fwd(*common, ws.data_ptr(), ws_bytes, stream)
+        rc = lib.b200sft_flce_fwd(*head, None, *outs, ws.data_ptr(), ws_bytes, stream)   # None: all N rows live
     assert rc == 0, lib.b200sft_last_error().decode()
     torch.cuda.synchronize(dev)
     return loss, lse, n_valid

@@ -134,16 +134,61 @@ def build_model(device: torch.device, attn: str, layers: int | None = None):
     return model
 
 
-def synthetic_window(step: int, ga: int, B: int, T: int, pin: bool):
-    """GA micro-batches of full-length rows: ids ~ U[0,V), labels = ids (every position trains)."""
+def _sample_lengths(g: torch.Generator, n: int, lo: int, hi: int):
+    """Variable sample lengths ~ LogNormal(median 420 tokens, sigma 0.6), clipped to [lo, hi]: a
+    stand-in for the tokenised-length distribution of data/qa_dataset.parquet (no tokenizer offline)."""
+    z = torch.randn(n, generator=g) * 0.6 + 6.04
+    return z.exp().clamp(lo, hi).long().tolist()
+
+
+def synthetic_window(step: int, ga: int, B: int, T: int, pin: bool, workload: str = "full"):
+    """GA micro-batches as dicts of host tensors (pinned when ``pin``).
+
+    full   -- full-length rows: ids ~ U[0,V), labels = ids (every position trains).
+    padded -- the reference collator's shape: variable-length rows right-padded to T, attention_mask 0
+              and labels -100 on the padding (the only mask the reference produces).
+    packed -- BASELINE config 5: variable-length samples packed into rows of T tokens, flattened to
+              [1, B*T] with restarting position_ids, -100 at the first token of every sample
+              (SP/transformers/data/data_collator.py:1426-1428) and FA2 varlen cu_seq_lens.
+    """
     g = torch.Generator().manual_seed(1234 + step)
     out = []
     for _ in range(ga):
         ids = torch.randint(0, V, (B, T), generator=g, dtype=torch.int64)
+        mb = {"input_ids": ids, "labels": ids.clone()}
+        if workload == "padded":
+            lens = _sample_lengths(g, B, 48, T)
+            mask = (torch.arange(T)[None, :] < torch.tensor(lens)[:, None]).long()
+            mb["attention_mask"] = mask
+            mb["labels"] = torch.where(mask.bool(), ids, torch.full_like(ids, -100))
+        elif workload == "packed":
+            pos = torch.empty(B, T, dtype=torch.int64)
+            labels = ids.clone()
+            cu = [0]
+            for r in range(B):
+                filled = 0
+                while filled < T:
+                    n = min(_sample_lengths(g, 1, 48, 1024)[0], T - filled)
+                    pos[r, filled:filled + n] = torch.arange(n)
+                    labels[r, filled] = -100
+                    filled += n
+                    cu.append(r * T + filled)
+            mb = {"input_ids": ids.reshape(1, B * T), "labels": labels.reshape(1, B * T),
+                  "position_ids": pos.reshape(1, B * T),
+                  "cu_seq_lens_q": torch.tensor(cu, dtype=torch.int32), "cu_seq_lens_k": torch.tensor(cu, dtype=torch.int32),
+                  "max_length_q": int(max(b - a for a, b in zip(cu[:-1], cu[1:]))),
+                  "max_length_k": int(max(b - a for a, b in zip(cu[:-1], cu[1:])))}
         if pin:
-            ids = ids.pin_memory()
-        out.append(ids)
+            mb = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in mb.items()}
+        out.append(mb)
     return out
+
+
+def window_tokens(window) -> tuple:
+    """(trained tokens, valid-label tokens) of a window: attention_mask.sum() (all tokens when absent)."""
+    trained = sum(int(mb["attention_mask"].sum()) if "attention_mask" in mb else mb["input_ids"].numel() for mb in window)
+    valid = sum(int(mb["labels"].ne(-100).sum()) for mb in window)
+    return trained, valid
 
 
 # ------------------------------------------------------------------------------------------
@@ -188,15 +233,15 @@ def run_b200(args) -> dict:
 
     def opt_step(window_dev) -> torch.Tensor:
         """One optimizer step on device-resident micro-batches; returns the summed loss."""
-        n_items = sum(ids.ne(-100).sum() for ids in window_dev)  # Trainer._get_num_items_in_batch
+        n_items = sum(mb["labels"].ne(-100).sum() for mb in window_dev)  # Trainer._get_num_items_in_batch
         if world > 1:
             dist.all_reduce(n_items)
         total_loss = torch.zeros((), device=dev)
-        for i, ids in enumerate(window_dev):
+        for i, mb in enumerate(window_dev):
             last = i == len(window_dev) - 1
             ctx = contextlib.nullcontext() if (last or world == 1) else wrapped.no_sync()
             with ctx:
-                loss = seam.compute_loss(wrapped, {"input_ids": ids, "labels": ids}, num_items_in_batch=n_items)
+                loss = seam.compute_loss(wrapped, dict(mb), num_items_in_batch=n_items)
                 loss.backward()
             total_loss += loss.detach()
         torch.nn.utils.clip_grad_norm_(params, 1.0)
@@ -204,10 +249,17 @@ def run_b200(args) -> dict:
         opt.zero_grad(set_to_none=True)
         return total_loss
 
+    to_dev = lambda mb: {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) else v) for k, v in mb.items()}
+    token_counts = {}
+
     def timed(steps: int, e2e: bool, first_step: int):
-        windows = [synthetic_window(first_step + s, GA, B, T, pin=e2e) for s in range(steps)]
+        # every rank draws its own data (seed offset by rank), as a sharded sampler would hand it out
+        windows = [synthetic_window((first_step + s) * 64 + rank, GA, B, T, pin=e2e, workload=args.workload)
+                   for s in range(steps)]
+        counts = [window_tokens(w) for w in windows]
+        token_counts[first_step] = (sum(c[0] for c in counts), sum(c[1] for c in counts))
         if not e2e:
-            windows = [[ids.to(dev) for ids in w] for w in windows]
+            windows = [[to_dev(mb) for mb in w] for w in windows]
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -217,7 +269,7 @@ def run_b200(args) -> dict:
         last_loss = None
         for w in windows:
             if e2e:
-                w = [ids.to(dev, non_blocking=True) for ids in w]   # H2D of the step's inputs (pinned)
+                w = [to_dev(mb) for mb in w]                        # H2D of the step's inputs (pinned)
             loss = opt_step(w)
             if e2e:
                 last_loss = loss.item()                             # D2H of the step's result
@@ -248,9 +300,19 @@ def run_b200(args) -> dict:
         ms_e2e, wall_e2e, last_loss = timed(args.steps, e2e=True, first_step=200)
     clocks = sampler.stop() if rank == 0 else None
 
-    tokens_per_step = B * T * GA * world
+    def all_ranks(x: float) -> float:
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t)
+        return float(t)
+
+    trained_dev, valid_dev = (all_ranks(v) for v in token_counts[100])
+    tokens_per_step = trained_dev / args.steps
     value = tokens_per_step / (ms_step / 1e3)
-    e2e_value = tokens_per_step / (ms_e2e / 1e3)
+    if args.no_e2e:
+        e2e_value = float("nan")
+    else:
+        e2e_value = all_ranks(token_counts[200][0]) / args.steps / (ms_e2e / 1e3)
     N = B * T
     peaks = read_peaks()
     fwd_flops = 2.0 * N * H * V
@@ -259,6 +321,8 @@ def run_b200(args) -> dict:
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get("flce_fwd_dram_bytes_per_launch")
+    probe = synthetic_window(0, GA, B, T, pin=False, workload=args.workload)
+    h2d_bytes = sum(v.numel() * v.element_size() for mb in probe for v in mb.values() if torch.is_tensor(v))
     res = {
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": round(ms_step, 3), "higher_is_better": True,
@@ -268,13 +332,19 @@ def run_b200(args) -> dict:
                         "freeze policy last-2-layers+tied lm_head, gradient checkpointing, fused LM-head+CE (sm_100a), "
                         "clip 1.0, fused AdamW" + (", DDP bucket 50 MiB + b200 comm hook" if world > 1 else ""),
             "global_batch": B * GA * world, "seq_len": T, "parallelism": f"dp{world}", "attn": attn,
+            "rows": {"full": "full-length rows, every position trains",
+                     "padded": "variable-length rows right-padded to seq_len (reference collator), -100 on padding",
+                     "packed": "variable-length samples packed to seq_len, flattened [1, B*T], restarting position_ids, "
+                               "-100 at sample starts, FA2 varlen"}[args.workload],
+            "tokens_per_step": round(tokens_per_step, 1), "valid_label_tokens_per_step": round(valid_dev / args.steps, 1),
+            "skip_ignored_rows": True,
             "layers": model.config.num_hidden_layers, "trainable_params": trainable, "total_params": total,
             "l2": "working set (6.2 GB of weights + activations per pass) far exceeds the 126 MB L2; no explicit flush",
             "attention_mask": "None (full-length rows; identical to an all-ones mask)",
         },
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "ms_per_step": round(ms_e2e, 3),
-                "h2d_bytes_per_step": B * T * 8 * GA, "d2h_bytes_per_step": 4,
+                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4,
                 "note": "pinned int64 input_ids copied H2D each step; summed loss read back with .item()",
                 "last_loss": last_loss},
         "gpu_launches": launches,
@@ -377,6 +447,8 @@ def main():
     ap.add_argument("--ga", type=int, default=2)
     ap.add_argument("--layers", type=int, default=None, help="debug only: fewer decoder layers (invalid as a result)")
     ap.add_argument("--attn", default="auto")
+    ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
+                    help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
     ap.add_argument("--cpu-tokens", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")

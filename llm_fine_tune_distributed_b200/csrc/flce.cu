@@ -48,7 +48,8 @@ struct FwdSoftmaxEpi {
   float run_m, run_s, run_ez;
   int lbl, row;
 
-  __device__ FwdSoftmaxEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {}
+  __device__ FwdSoftmaxEpi(const Params& p_, const GemmShape& s, uint8_t*) : p(p_), M(s.M), N(s.N) {}
+  __device__ __forceinline__ void finish() {}
 
   __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) {
     row = tc.m0 + row_in_tile;
@@ -117,6 +118,58 @@ struct FwdSoftmaxEpi {
   }
 };
 
+// ---- bf16 output staging: registers -> swizzled smem -> TMA store ---------------------------------
+// Each epilogue thread owns one output row and produces 32 consecutive columns per chunk.  Writing
+// those straight to global memory makes every warp store touch 32 different lines; instead the warp
+// stages a [32 rows x 64 columns] block in shared memory (128-byte rows, 128B swizzle: 16-byte piece
+// j of row r sits at position j ^ (r & 7), conflict-free for the quarter-warp wavefronts) and one
+// lane issues a TMA store for it.  The TMA unit clips the box at the tensor's edges, so ragged
+// last tiles need no special handling.
+struct Bf16TileStore {
+  uint8_t* smem;  // this warp's EPI_WARP_SMEM_BYTES
+  int lane;
+
+  __device__ __forceinline__ void init(uint8_t* warp_smem) {
+    smem = warp_smem;
+    lane = threadIdx.x & 31;
+  }
+
+  // `half` = which 32-column half of the 64-column block these values fill.
+  __device__ __forceinline__ void stage(const float (&g)[32], int half) {
+    if (half == 0) {  // the block buffer is about to be overwritten: the previous store must have read it
+      if (lane == 0) tma_store_wait_read<0>();
+      __syncwarp();
+    }
+    uint8_t* row = smem + lane * 128;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 v;
+      v.x = pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1]);
+      v.y = pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3]);
+      v.z = pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5]);
+      v.w = pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]);
+      const int piece = (half * 4 + q) ^ (lane & 7);
+      *reinterpret_cast<uint4*>(row + piece * 16) = v;
+    }
+  }
+
+  // Store the staged block to global (col0 = first column of the 64-column block, row0 = first of
+  // the warp's 32 rows).  Columns / rows beyond the tensor map's extents are not written.
+  __device__ __forceinline__ void flush(const CUtensorMap* map, int col0, int row0) {
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(map, smem, col0, row0);
+      tma_store_commit();
+    }
+  }
+
+  __device__ __forceinline__ void drain() {
+    if (lane == 0) tma_store_wait<0>();
+    __syncwarp();
+  }
+};
+
 // ---- backward stage 1: dlogits tile -> bf16 scratch --------------------------------------------
 struct DlogitsEpi {
   struct Params {
@@ -127,22 +180,24 @@ struct DlogitsEpi {
     float scale;
     int ignore_index;
     int round_bf16;
-    __nv_bfloat16* out;  // [M][ld]: this vocabulary slab of dlogits
-    int ld;
-    int col_offset;  // first vocabulary column of the slab (labels are global column indices)
-    int rows_alloc;  // rows the scratch holds; rows in [live rows, rows_alloc) are written as zeros
-                     // because the dW GEMM contracts over them in whole 64-row blocks
+    CUtensorMap out_map;  // [rows_alloc][slab cols] bf16 view of this vocabulary slab of dlogits, box 64 x 32.
+                          // Rows in [live rows, rows_alloc) are written as zeros because the dW GEMM
+                          // contracts over them in whole 64-row blocks.
+    int col_offset;       // first vocabulary column of the slab (labels are global column indices)
   };
   const Params& p;
   const int M, N;
   float coef_all, coef, lse2;
   int lbl, row;  // lbl is slab-local: label - col_offset (never matches when outside the slab)
+  Bf16TileStore st;
 
-  __device__ DlogitsEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {
+  __device__ DlogitsEpi(const Params& p_, const GemmShape& s, uint8_t* warp_smem) : p(p_), M(s.M), N(s.N) {
     float c = __ldg(p.grad_out) * p.scale;
     if (p.denom != nullptr) c = c / static_cast<float>(__ldg(p.denom));
     coef_all = c;
+    st.init(warp_smem);
   }
+  __device__ __forceinline__ void finish() { st.drain(); }
 
   __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) {
     row = tc.m0 + row_in_tile;
@@ -156,9 +211,9 @@ struct DlogitsEpi {
     lbl = glbl - p.col_offset;
   }
 
-  __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
+  __device__ __forceinline__ void chunk(const TileCoord& tc, int row_in_tile, int c, const uint32_t (&acc)[32]) {
     const int col0 = tc.n0 + c;
-    if (col0 >= N || row >= p.rows_alloc) return;
+    if (col0 >= N) return;  // warp-uniform
     float g[32];
     if (coef == 0.f) {  // ignored / dead row (or zero upstream gradient): exact zeros
 #pragma unroll
@@ -173,23 +228,10 @@ struct DlogitsEpi {
         g[j] = pr * coef;
       }
     }
-    __nv_bfloat16* dst = p.out + static_cast<size_t>(row) * p.ld + col0;
-    if (col0 + 32 <= N) {
-      uint4* d4 = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 v;
-        v.x = pack_bf16x2(g[q * 8 + 0], g[q * 8 + 1]);
-        v.y = pack_bf16x2(g[q * 8 + 2], g[q * 8 + 3]);
-        v.z = pack_bf16x2(g[q * 8 + 4], g[q * 8 + 5]);
-        v.w = pack_bf16x2(g[q * 8 + 6], g[q * 8 + 7]);
-        d4[q] = v;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) dst[j] = __float2bfloat16_rn(g[j]);
-    }
+    const int half = (c >> 5) & 1;
+    st.stage(g, half);
+    if (half == 1 || col0 + 32 >= N)  // block complete, or the slab ends inside it
+      st.flush(&p.out_map, col0 - half * 32, tc.m0 + (row_in_tile & ~31));
   }
 
   __device__ __forceinline__ void tile_end(const TileCoord&, int) {}
@@ -200,29 +242,31 @@ enum StoreMode { STORE_BF16 = 0, STORE_F32 = 1, ACCUM_F32 = 2, ACCUM_F32_OUT_BF1
 
 struct StoreEpi {
   struct Params {
-    __nv_bfloat16* out;  // [M][ld] bf16 (modes 0, 3)
-    float* acc;          // [M][ld] fp32 (modes 1, 2, 3)
+    CUtensorMap out_map;  // [rows][cols] bf16 output view, box 64 x 32 (modes 0, 3)
+    float* acc;           // [M][ld] fp32 (modes 1, 2, 3)
     int ld;
     int mode;
   };
   const Params& p;
   const int M, N;
   int row;
+  Bf16TileStore st;
 
-  __device__ StoreEpi(const Params& p_, const GemmShape& s) : p(p_), M(s.M), N(s.N) {}
+  __device__ StoreEpi(const Params& p_, const GemmShape& s, uint8_t* warp_smem) : p(p_), M(s.M), N(s.N) {
+    st.init(warp_smem);
+  }
   __device__ __forceinline__ void tile_begin(const TileCoord& tc, int row_in_tile) { row = tc.m0 + row_in_tile; }
+  __device__ __forceinline__ void finish() { st.drain(); }
 
-  __device__ __forceinline__ void chunk(const TileCoord& tc, int, int c, const uint32_t (&acc)[32]) {
+  __device__ __forceinline__ void chunk(const TileCoord& tc, int row_in_tile, int c, const uint32_t (&acc)[32]) {
     const int col0 = tc.n0 + c;
-    if (col0 >= N || row >= M) return;
-    const size_t off = static_cast<size_t>(row) * p.ld + col0;
+    if (col0 >= N) return;  // warp-uniform
     float v[32];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-    const bool full = (col0 + 32 <= N);
-    if (p.mode != STORE_BF16) {
-      float* a = p.acc + off;
-      if (full) {
+    for (int j = 0; j < 32; ++j) v[j] = (row < M) ? __uint_as_float(acc[j]) : 0.f;
+    if (p.mode != STORE_BF16 && row < M) {  // fp32 accumulator across launches (only used with long K: cheap)
+      float* a = p.acc + static_cast<size_t>(row) * p.ld + col0;
+      if (col0 + 32 <= N) {
         float4* a4 = reinterpret_cast<float4*>(a);
         if (p.mode != STORE_F32) {
 #pragma unroll
@@ -249,23 +293,9 @@ struct StoreEpi {
       }
     }
     if (p.mode == STORE_BF16 || p.mode == ACCUM_F32_OUT_BF16) {
-      __nv_bfloat16* dst = p.out + off;
-      if (full) {
-        uint4* d4 = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 t;
-          t.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
-          t.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-          t.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
-          t.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-          d4[q] = t;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < N) dst[j] = __float2bfloat16_rn(v[j]);
-      }
+      const int half = (c >> 5) & 1;
+      st.stage(v, half);
+      if (half == 1 || col0 + 32 >= N) st.flush(&p.out_map, col0 - half * 32, tc.m0 + (row_in_tile & ~31));
     }
   }
   __device__ __forceinline__ void tile_end(const TileCoord&, int) {}
@@ -478,6 +508,11 @@ int make_tmap(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, 
 int make_operand_tmap(CUtensorMap* m, const void* base, int rows, int K, int ld, bool mn_major, int block_rows) {
   if (!mn_major) return make_tmap(m, base, K, rows, ld, BLOCK_K, block_rows);
   return make_tmap(m, base, rows, K, ld, 64, BLOCK_K);
+}
+
+// Output view for the epilogue's TMA stores: [rows][cols] bf16, row pitch ld, box = 64 columns x 32 rows.
+int make_store_tmap(CUtensorMap* m, const void* base, int rows, int cols, int ld) {
+  return make_tmap(m, base, static_cast<uint64_t>(cols), static_cast<uint64_t>(rows), static_cast<uint64_t>(ld), 64, 32);
 }
 
 int num_sms() {
@@ -756,16 +791,16 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     dp.scale = scale;
     dp.ignore_index = ignore_index;
     dp.round_bf16 = (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0;
-    dp.out = dlog;
-    dp.ld = slab;
+    rc = make_store_tmap(&dp.out_map, dlog, N, cols, slab);
+    if (rc != 0) return rc;
     dp.col_offset = v0;
-    dp.rows_alloc = N;
     rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream, n_rows_dev, 0);
     if (rc != 0) return rc;
 
     // (2) dX[N,H] (+)= dlogits[N,cols] . W[v0:v0+cols, :]     A K-major, B = W rows read MN-major
     StoreEpi::Params sx;
-    sx.out = static_cast<__nv_bfloat16*>(dx);
+    rc = make_store_tmap(&sx.out_map, dx, N, H, H);
+    if (rc != 0) return rc;
     sx.acc = dx_acc;
     sx.ld = H;
     if (num_slabs == 1)
@@ -782,7 +817,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every
     //     row, so each dW slab is final after one GEMM (no accumulation across slabs)
     StoreEpi::Params sw;
-    sw.out = dwb + static_cast<size_t>(v0) * H;
+    rc = make_store_tmap(&sw.out_map, dwb + static_cast<size_t>(v0) * H, cols, H, H);
+    if (rc != 0) return rc;
     sw.acc = nullptr;
     sw.ld = H;
     sw.mode = STORE_BF16;
@@ -798,7 +834,8 @@ int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K
   if (!a || !b || !c) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
   if (ldc % 8 != 0) return fail(B200SFT_ERR_INVALID, "ldc must be a multiple of 8");
   StoreEpi::Params sp;
-  sp.out = static_cast<__nv_bfloat16*>(c);
+  int rc = make_store_tmap(&sp.out_map, c, M, N, ldc);
+  if (rc != 0) return rc;
   sp.acc = nullptr;
   sp.ld = ldc;
   sp.mode = STORE_BF16;

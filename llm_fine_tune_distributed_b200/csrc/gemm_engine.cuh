@@ -29,7 +29,11 @@ constexpr int TMEM_COLS = NUM_ACC_STAGES * BLOCK_N;  // 512: the whole TMEM of t
 constexpr int NUM_EPI_WARPS = 4;
 constexpr int GEMM_THREADS = 32 * (2 + NUM_EPI_WARPS);
 constexpr int SMEM_BARRIER_BYTES = 256;
-constexpr int GEMM_SMEM_BYTES = NUM_STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + SMEM_BARRIER_BYTES;
+// Per-epilogue-warp staging tile for TMA stores: 32 rows x 128 B (64 bf16 columns), 128B-swizzled.
+constexpr int EPI_WARP_SMEM_BYTES = 32 * 128;
+constexpr int EPI_SMEM_BYTES = NUM_EPI_WARPS * EPI_WARP_SMEM_BYTES;
+constexpr int GEMM_SMEM_BYTES =
+    NUM_STAGES * STAGE_BYTES + EPI_SMEM_BYTES + 1024 /*alignment slack*/ + SMEM_BARRIER_BYTES;
 
 struct GemmShape {
   int M, N, K;
@@ -69,16 +73,18 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
 
 // Epilogue contract:
 //   struct Epi { struct Params {...};
-//     __device__ Epi(const Params&, const GemmShape&);
+//     __device__ Epi(const Params&, const GemmShape&, uint8_t* warp_smem /*EPI_WARP_SMEM_BYTES, 1024-aligned*/);
 //     // called by each of the 128 epilogue threads; `row_in_tile` = TMEM lane owned by the thread
 //     __device__ void tile_begin(const TileCoord&, int row_in_tile);
 //     __device__ void chunk(const TileCoord&, int row_in_tile, int col_in_tile /*0,32,..*/, const uint32_t (&acc)[32]);
 //     __device__ void tile_end(const TileCoord&, int row_in_tile);
+//     __device__ void finish();   // once per thread after the last tile (drain outstanding TMA stores)
 //   };
+// Params is a __grid_constant__ kernel parameter, so it may embed CUtensorMaps for TMA stores.
 template <class Epi, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                        const GemmShape shape_in, const typename Epi::Params epi_params) {
+                        const GemmShape shape_in, const __grid_constant__ typename Epi::Params epi_params) {
   GemmShape shape = shape_in;
   if (shape.dyn_rows != nullptr) {
     int r = __ldg(shape.dyn_rows);
@@ -95,7 +101,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + NUM_STAGES * A_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES);
+  uint8_t* smem_epi = smem + NUM_STAGES * STAGE_BYTES;  // 1024-aligned: NUM_STAGES * STAGE_BYTES is a multiple of 1024
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NUM_STAGES * STAGE_BYTES + EPI_SMEM_BYTES);
   uint64_t* full_bar = bars;                                    // [NUM_STAGES]  TMA -> MMA
   uint64_t* empty_bar = bars + NUM_STAGES;                      // [NUM_STAGES]  MMA -> TMA
   uint64_t* acc_full_bar = bars + 2 * NUM_STAGES;               // [2] MMA -> epilogue
@@ -204,7 +211,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     // ------------------------------- epilogue warps -------------------------------
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
     const int row_in_tile = quarter * 32 + lane;
-    Epi epi(epi_params, shape);
+    Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const TileCoord tc = tile_coord(shape, tile);
@@ -232,6 +239,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       if (lane == 0) mbar_arrive(&acc_empty_bar[as]);
       epi.tile_end(tc, row_in_tile);
     }
+    epi.finish();
   }
 
   tc_fence_before_sync();

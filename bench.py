@@ -196,7 +196,8 @@ def window_tokens(window) -> tuple:
 # ------------------------------------------------------------------------------------------
 def run_b200(args) -> dict:
     from llm_fine_tune_distributed_b200 import ops
-    from llm_fine_tune_distributed_b200.comm_hook import B200HookState, b200_allreduce_hook
+    from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, B200NvlinkState, b200_allreduce_hook,
+                                                          b200_nvlink_allreduce_hook)
     from llm_fine_tune_distributed_b200.loss import FusedCELossMixin, install_fused_head
     from llm_fine_tune_distributed_b200.training import apply_freeze_policy
 
@@ -218,8 +219,12 @@ def run_b200(args) -> dict:
     if world > 1:
         wrapped = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], bucket_cap_mb=50,
                                                             find_unused_parameters=False)
-        hook_state = B200HookState(None)
-        wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
+        if args.comm == "nvlink":
+            hook_state = B200NvlinkState.for_model(model, None)
+            wrapped.register_comm_hook(hook_state, b200_nvlink_allreduce_hook)
+        else:
+            hook_state = B200HookState(None)
+            wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
         wrapped._b200sft_hook = True
     params = [p for p in model.parameters() if p.requires_grad]
     opt = torch.optim.AdamW(params, lr=5e-5 * world, weight_decay=0.0, fused=True)
@@ -307,6 +312,26 @@ def run_b200(args) -> dict:
         return float(t)
 
     trained_dev, valid_dev = (all_ranks(v) for v in token_counts[100])
+    if args.kernel_table and rank == 0:
+        from torch.profiler import ProfilerActivity, profile
+
+        win = [to_dev(mb) for mb in synthetic_window(999 * 64 + rank, GA, B, T, pin=False, workload=args.workload)]
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            opt_step(win)
+            torch.cuda.synchronize()
+        rows = [(e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0
+                and e.device_type == torch.autograd.DeviceType.CUDA]
+        rows.sort(key=lambda r: -r[2])
+        tot = sum(r[2] for r in rows) or 1.0
+        ours = sum(r[2] for r in rows if "b200::" in r[0])
+        with open(args.kernel_table, "w") as f:
+            f.write("# Kernel device-time table of one bench.py optimizer step (torch.profiler / CUPTI)\n\n"
+                    f"workload {args.workload}, B={B} T={T} GA={GA}, {model.config.num_hidden_layers} layers; "
+                    f"total kernel time {tot / 1e3:.2f} ms; this library's kernels {ours / 1e3:.2f} ms "
+                    f"({100 * ours / tot:.1f} %)\n\n| kernel | launches | total ms | share |\n|---|---:|---:|---:|\n")
+            for k, n, t in rows[:45]:
+                f.write(f"| `{k[:110]}` | {n} | {t / 1e3:.3f} | {100 * t / tot:.1f}% |\n")
     tokens_per_step = trained_dev / args.steps
     value = tokens_per_step / (ms_step / 1e3)
     if args.no_e2e:
@@ -330,7 +355,7 @@ def run_b200(args) -> dict:
         "config": {
             "workload": f"SmolLM3-3B random-init bf16 SFT optimizer step: seq {T}, per-device batch {B}, grad-accum {GA}, "
                         "freeze policy last-2-layers+tied lm_head, gradient checkpointing, fused LM-head+CE (sm_100a), "
-                        "clip 1.0, fused AdamW" + (", DDP bucket 50 MiB + b200 comm hook" if world > 1 else ""),
+                        "clip 1.0, fused AdamW" + (f", DDP bucket 50 MiB + b200 comm hook ({args.comm})" if world > 1 else ""),
             "global_batch": B * GA * world, "seq_len": T, "parallelism": f"dp{world}", "attn": attn,
             "rows": {"full": "full-length rows, every position trains",
                      "padded": "variable-length rows right-padded to seq_len (reference collator), -100 on padding",
@@ -362,8 +387,10 @@ def run_b200(args) -> dict:
         "wall_s": {"device_timed": round(wall_dev, 3), "e2e_timed": round(wall_e2e, 3)},
     }
     if hook_state is not None:
-        res["comm"] = {"buckets_per_step": hook_state.buckets_seen / max(args.steps * 2 + max(args.warmup, 3), 1),
-                       "bytes_reduced_total": hook_state.bytes_reduced}
+        n_steps = args.steps * (1 if args.no_e2e else 2) + max(args.warmup, 3)
+        res["comm"] = {"hook": args.comm, "path": getattr(hook_state, "path_used", "nccl"),
+                       "buckets_per_step": round(hook_state.buckets_seen / max(n_steps, 1), 2),
+                       "bytes_reduced_per_step": round(hook_state.bytes_reduced / max(n_steps, 1))}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"] = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=1)
     if world > 1:
@@ -447,11 +474,17 @@ def main():
     ap.add_argument("--ga", type=int, default=2)
     ap.add_argument("--layers", type=int, default=None, help="debug only: fewer decoder layers (invalid as a result)")
     ap.add_argument("--attn", default="auto")
+    ap.add_argument("--comm", default="nccl", choices=["nccl", "nvlink"],
+                    help="N>1: gradient hook = scale kernel + NCCL allreduce (default), or this library's fused "
+                         "NVLink reduce+scale kernel over symmetric memory")
     ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
                     help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
     ap.add_argument("--cpu-tokens", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")
+    ap.add_argument("--kernel-table", default=None, metavar="PATH",
+                    help="after the timed passes, trace ONE more step with torch.profiler (CUPTI) and write the "
+                         "per-kernel device-time table (markdown) to PATH")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus != world and world == 1 and args.gpus > 1:

@@ -182,6 +182,24 @@ int b200sft_scale_f32_inplace(float* buf, size_t n, float scale, void* stream);
 int b200sft_scale_cast_f32_to_bf16(const float* src, void* dst, size_t n, float scale, void* stream);
 int b200sft_cast_bf16_to_f32(const void* src, float* dst, size_t n, float scale, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Bucket allreduce over NVLink 5 / NVSwitch with the scale fused in: one pass that reduces a bf16
+ * bucket across ranks (fp32 accumulate), multiplies by `scale` (1/world) and leaves the result in
+ * every rank's copy.  Replaces the div_ + ncclAllReduce pair of default_hooks.py:18-32 for buckets
+ * held in symmetric memory (torch.distributed._symmetric_memory).
+ *   multimem: `multicast_ptr` is the NVLS multicast address of the bucket (multimem.ld_reduce /
+ *             multimem.st: the reduction and the broadcast happen inside the switch);
+ *   p2p:      `peer_ptrs_host` is a HOST array of `world` device pointers, the bucket's address on
+ *             each rank (own rank included), for boxes without multicast support.
+ * Each rank processes slice `rank` of `world` equal slices; n (elements) must be a multiple of
+ * 8*world.  The kernels never wait on another rank: the caller must order them across ranks with a
+ * symmetric-memory barrier before (all copies written) and after (all results written) the call.
+ */
+int b200sft_allreduce_scale_bf16_multimem(void* multicast_ptr, size_t n, int rank, int world, float scale,
+                                          void* stream);
+int b200sft_allreduce_scale_bf16_p2p(const uint64_t* peer_ptrs_host, size_t n, int rank, int world, float scale,
+                                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

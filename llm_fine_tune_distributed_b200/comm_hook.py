@@ -24,7 +24,8 @@ import torch.distributed as dist
 
 from . import ops
 
-__all__ = ["B200HookState", "b200_allreduce_hook", "b200_bf16_compress_hook", "register_b200_comm_hook"]
+__all__ = ["B200HookState", "B200NvlinkState", "b200_allreduce_hook", "b200_bf16_compress_hook",
+           "b200_nvlink_allreduce_hook", "register_b200_comm_hook"]
 
 
 class B200HookState:
@@ -110,9 +111,123 @@ def b200_bf16_compress_hook(state: B200HookState, bucket: dist.GradBucket) -> to
     return work.get_future().then(decompress)
 
 
+class B200NvlinkState(B200HookState):
+    """State for :func:`b200_nvlink_allreduce_hook`: ONE symmetric-memory arena
+    (``torch.distributed._symmetric_memory``: every rank maps every peer's copy, plus an NVLS
+    multicast address when the fabric supports it) sized for all gradients of the model, allocated
+    and exchanged here -- a collective, so construct the state on every rank at the same point,
+    before training.  Buckets are carved from the arena in arrival order during each backward, so
+    the hook itself performs no allocation and no host-side collective."""
+
+    def __init__(self, total_grad_elements: int, device: torch.device,
+                 process_group: Optional[dist.ProcessGroup] = None, use_multimem: Optional[bool] = None,
+                 max_buckets: int = 512):
+        super().__init__(process_group)
+        import torch.distributed._symmetric_memory as symm_mem
+
+        world = self.group().size()
+        self.align = 8 * world                       # elements: 16-byte vectors, one slice per rank
+        self.capacity = (int(total_grad_elements) + max_buckets * self.align + self.align - 1) // self.align * self.align
+        with torch.cuda.device(device):
+            self.arena = symm_mem.empty(self.capacity, dtype=torch.bfloat16, device=device)
+            self.handle = symm_mem.rendezvous(self.arena, self.group())
+        self.use_multimem = bool(self.handle.multicast_ptr) if use_multimem is None else bool(use_multimem)
+        self.path_used = "multimem" if self.use_multimem else "p2p"
+        self._offset = 0
+        self._seen = set()
+        self.trace = None  # set to a list to record (bucket index, numel, offset) per hook call (debugging)
+
+    @classmethod
+    def for_model(cls, model: torch.nn.Module, process_group: Optional[dist.ProcessGroup] = None, **kw):
+        params = [p for p in model.parameters() if p.requires_grad]
+        return cls(sum(p.numel() for p in params), params[0].device, process_group, **kw)
+
+    def carve(self, bucket_index: int, numel: int):
+        """(element offset, padded length) of this bucket inside the arena for the current backward."""
+        if bucket_index in self._seen:  # an index repeats: a new backward pass has started
+            self._seen.clear()
+            self._offset = 0
+        self._seen.add(bucket_index)
+        padded = (numel + self.align - 1) // self.align * self.align
+        off = self._offset
+        if off + padded > self.capacity:
+            raise RuntimeError(f"symmetric arena too small: need {off + padded} elements, have {self.capacity}")
+        self._offset = off + padded
+        if self.trace is not None:
+            self.trace.append((bucket_index, numel, off))
+        return off, padded
+
+
+class _DevicePtr:
+    """Minimal __cuda_array_interface__ carrier: lets torch alias `nbytes` of device memory at `ptr`
+    as a tensor whose storage starts exactly there."""
+
+    def __init__(self, ptr: int, n_int16: int):
+        self.__cuda_array_interface__ = {"shape": (n_int16,), "typestr": "<i2", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+def _alias_bf16(ptr: int, numel: int, device: torch.device) -> torch.Tensor:
+    # DDP builds its per-parameter views of a hook's result with as_strided(sizes, strides, offset)
+    # where `offset` is relative to the bucket start, i.e. it assumes storage_offset == 0
+    # (Reducer::initialize_bucket_views).  A plain slice of the arena would therefore be read from
+    # the arena's start; alias the slice as a tensor with its own zero-offset storage instead.
+    return torch.as_tensor(_DevicePtr(ptr, numel), device=device).view(torch.bfloat16)
+
+
+def b200_nvlink_allreduce_hook(state: B200NvlinkState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+    """Average a bf16 gradient bucket with this library's own NVLink kernel: copy into the symmetric
+    arena, then ONE kernel reduces across ranks (in the NVSwitch via multimem when available, else
+    by peer loads), applies 1/world in registers and broadcasts the result to every rank.  The
+    future's value is the arena slice; DDP copies it back into the gradients.  Non-bf16 or CPU
+    buckets take the NCCL hook."""
+    buf = bucket.buffer()
+    if not buf.is_cuda or buf.dtype != torch.bfloat16:
+        return b200_allreduce_hook(state, bucket)
+    import ctypes
+
+    from . import _cabi
+
+    group = state.group()
+    world, rank, n = group.size(), group.rank(), buf.numel()
+    state.buckets_seen += 1
+    state.bytes_reduced += n * 2
+    off, padded = state.carve(bucket.index(), n)
+    hdl = state.handle
+    view = _alias_bf16(state.arena.data_ptr() + 2 * off, n, buf.device)  # same memory as arena[off:off+n]
+    lib = _cabi.load()
+    cur = torch.cuda.current_stream(buf.device)
+    side = state.side_stream(buf.device)
+    side.wait_stream(cur)
+    buf.record_stream(side)
+    with torch.cuda.device(buf.device), torch.cuda.stream(side):
+        view.copy_(buf)
+        hdl.barrier(channel=0)                      # every rank's copy is in place
+        if state.use_multimem:
+            _cabi.check(lib.b200sft_allreduce_scale_bf16_multimem(int(hdl.multicast_ptr) + 2 * off, padded, rank, world,
+                                                                  1.0 / world, side.cuda_stream),
+                        "b200sft_allreduce_scale_bf16_multimem")
+        else:
+            ptrs = (ctypes.c_uint64 * world)(*[int(p) + 2 * off for p in hdl.buffer_ptrs])
+            _cabi.check(lib.b200sft_allreduce_scale_bf16_p2p(ptrs, padded, rank, world, 1.0 / world, side.cuda_stream),
+                        "b200sft_allreduce_scale_bf16_p2p")
+        ops.STATS.kernel_launches += 1
+        hdl.barrier(channel=0)                      # every rank's slice of the result has landed everywhere
+        fut = torch.futures.Future(devices=[buf.device])
+        fut.set_result(view)
+    return fut
+
+
 def register_b200_comm_hook(ddp_model: torch.nn.parallel.DistributedDataParallel,
-                            state: Optional[B200HookState] = None, compress_fp32: bool = False) -> B200HookState:
-    """``ddp_model.register_comm_hook(state, hook)`` with this library's hook; returns the state."""
-    state = state or B200HookState(getattr(ddp_model, "process_group", None))
+                            state: Optional[B200HookState] = None, compress_fp32: bool = False,
+                            nvlink_kernel: bool = False) -> B200HookState:
+    """``ddp_model.register_comm_hook(state, hook)`` with this library's hook; returns the state.
+    ``nvlink_kernel`` selects the fused NVLink reduce+scale kernel instead of scale kernel + NCCL."""
+    pg = getattr(ddp_model, "process_group", None)
+    if nvlink_kernel:
+        state = state or B200NvlinkState.for_model(ddp_model.module, pg)
+        ddp_model.register_comm_hook(state, b200_nvlink_allreduce_hook)
+        return state
+    state = state or B200HookState(pg)
     ddp_model.register_comm_hook(state, b200_bf16_compress_hook if compress_fp32 else b200_allreduce_hook)
     return state

@@ -23,8 +23,8 @@ def _worker(rank, world, port, ret):
     from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
     from torch.nn.parallel import DistributedDataParallel as DDP
 
-    from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, b200_allreduce_hook,
-                                                          b200_bf16_compress_hook)
+    from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, B200NvlinkState, b200_allreduce_hook,
+                                                          b200_bf16_compress_hook, b200_nvlink_allreduce_hook)
 
     def run(dtype, hook):
         torch.manual_seed(0)
@@ -38,11 +38,14 @@ def _worker(rank, world, port, ret):
         elif hook == "b200_compress":
             state = B200HookState(None)
             ddp.register_comm_hook(state, b200_bf16_compress_hook)
+        elif hook in ("nvlink", "nvlink_p2p"):
+            state = B200NvlinkState.for_model(net, None, use_multimem=None if hook == "nvlink" else False)
+            ddp.register_comm_hook(state, b200_nvlink_allreduce_hook)
         elif hook == "torch_compress":
             ddp.register_comm_hook(None, default_hooks.bf16_compress_hook)
         g = torch.Generator().manual_seed(10 + rank)
         x = torch.randn(64, 512, generator=g).to(dev).to(dtype)
-        for _ in range(2):  # second iteration runs on DDP's rebuilt buckets
+        for _ in range(3):  # later iterations run on DDP's rebuilt buckets
             with ddp.no_sync():
                 ddp(x).float().pow(2).mean().backward()
             ddp(x * 0.5).float().pow(2).mean().backward()
@@ -54,6 +57,20 @@ def _worker(rank, world, port, ret):
     ours, st = run(torch.bfloat16, "b200")
     out["bf16_equal"] = all(torch.equal(a, b) for a, b in zip(stock, ours))
     out["buckets"] = st.buckets_seen
+    for name in ("nvlink", "nvlink_p2p"):
+        got, stn = run(torch.bfloat16, name)
+        # fp32 accumulation + one rounding vs NCCL's own order: equal to bf16 resolution, and bit-identical
+        # across ranks (every rank reads the same reduced copy)
+        # p2p: fp32 sum of two bf16 values, exact power-of-two scale, one rounding == NCCL's result bit for bit at
+        # world 2.  multimem: the NVSwitch's in-fabric reduction may round the last bf16 bit differently, and the
+        # test accumulates .grad over three iterations, so allow a few bf16 ulps there.
+        rtol, atol = (0.0, 0.0) if name == "nvlink_p2p" else (2.0 ** -5, 1e-4)
+        out[name + "_close"] = all(torch.allclose(a.float(), b.float(), rtol=rtol, atol=atol) for a, b in zip(stock, got))
+        flat = torch.cat([g.flatten().float() for g in got])
+        gathered = [torch.zeros_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        out[name + "_same_on_all_ranks"] = all(torch.equal(gathered[0], t) for t in gathered)
+        out[name + "_path"] = stn.path_used
     ref_c, _ = run(torch.float32, "torch_compress")
     ours_c, _ = run(torch.float32, "b200_compress")
     out["compress_equal"] = all(torch.equal(a, b) for a, b in zip(ref_c, ours_c))
@@ -70,3 +87,8 @@ def test_comm_hook_nccl_world2_matches_stock_ddp():
         assert ret[r]["bf16_equal"], "bf16 bucket path differs from stock DDP"
         assert ret[r]["compress_equal"], "fp32 compress path differs from torch's bf16_compress_hook"
         assert ret[r]["buckets"] >= 2
+        for name in ("nvlink", "nvlink_p2p"):
+            assert ret[r][name + "_close"], f"{name}: differs from stock DDP beyond bf16 resolution"
+            assert ret[r][name + "_same_on_all_ranks"], f"{name}: ranks disagree"
+        assert ret[r]["nvlink_p2p_path"] == "p2p"
+    print("nvlink hook path:", ret[0]["nvlink_path"])

@@ -131,7 +131,10 @@ class B200NvlinkState(B200HookState):
         with torch.cuda.device(device):
             self.arena = symm_mem.empty(self.capacity, dtype=torch.bfloat16, device=device)
             self.handle = symm_mem.rendezvous(self.arena, self.group())
-        self.use_multimem = bool(self.handle.multicast_ptr) if use_multimem is None else bool(use_multimem)
+        # measured on 8xB200 (profiles/r01_allreduce_microbench.jsonl): the in-switch (NVLS) reduction wins from
+        # 4 ranks up; with 2 ranks plain peer loads are faster (each rank pulls half a bucket over one hop)
+        auto = bool(self.handle.multicast_ptr) and world > 2
+        self.use_multimem = auto if use_multimem is None else bool(use_multimem)
         self.path_used = "multimem" if self.use_multimem else "p2p"
         self._offset = 0
         self._seen = set()

@@ -37,27 +37,50 @@ __device__ __forceinline__ uint32_t scale_packed(uint32_t v, float s) {
   return f2_to_bf16x2(f.x * s, f.y * s);
 }
 
+constexpr int AR_UNROLL = 4;  // independent 16-byte multimem / peer accesses in flight per thread
+
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const uint4* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_b128(uint4* p, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
 // nvec = number of 16-byte vectors (8 bf16) in the bucket; must be a multiple of `world`.
+// Block-contiguous chunks (as the streaming kernels in elementwise.cu): per pass a block owns
+// AR_UNROLL * blockDim consecutive vectors of this rank's slice.
 __global__ void __launch_bounds__(512)
     allreduce_scale_multimem_bf16_kernel(uint4* mc, size_t nvec, int rank, int world, float scale) {
   const size_t per = nvec / world;
   uint4* base = mc + static_cast<size_t>(rank) * per;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < per;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    uint32_t a, b, c, d;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
-                 : "l"(base + i)
-                 : "memory");
-    if (scale != 1.0f) {
-      a = scale_packed(a, scale);
-      b = scale_packed(b, scale);
-      c = scale_packed(c, scale);
-      d = scale_packed(d, scale);
+  const size_t chunk = static_cast<size_t>(blockDim.x) * AR_UNROLL;
+  for (size_t c0 = blockIdx.x * chunk; c0 < per; c0 += static_cast<size_t>(gridDim.x) * chunk) {
+    uint4 v[AR_UNROLL];
+#pragma unroll
+    for (int u = 0; u < AR_UNROLL; ++u) {
+      const size_t i = c0 + threadIdx.x + u * blockDim.x;
+      if (i < per) v[u] = multimem_ld_reduce_bf16x8(base + i);
     }
-    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(base + i), "r"(a), "r"(b),
-                 "r"(c), "r"(d)
-                 : "memory");
+#pragma unroll
+    for (int u = 0; u < AR_UNROLL; ++u) {
+      const size_t i = c0 + threadIdx.x + u * blockDim.x;
+      if (i < per) {
+        if (scale != 1.0f) {
+          v[u].x = scale_packed(v[u].x, scale);
+          v[u].y = scale_packed(v[u].y, scale);
+          v[u].z = scale_packed(v[u].z, scale);
+          v[u].w = scale_packed(v[u].w, scale);
+        }
+        multimem_st_b128(base + i, v[u]);
+      }
+    }
   }
 }
 
@@ -71,7 +94,7 @@ __global__ void __launch_bounds__(512)
   const size_t per = nvec / world;
   const size_t first = static_cast<size_t>(rank) * per;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < per;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {  // consecutive blocks take consecutive 8 KiB runs
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     uint4 v[MAX_PEERS];
 #pragma unroll
@@ -108,7 +131,7 @@ int ar_grid(size_t per_rank_vecs, int threads) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (sms <= 0) sms = 148;
   size_t blocks = (per_rank_vecs + threads - 1) / threads;
-  const size_t cap = static_cast<size_t>(sms) * 4;  // leaves SMs to the backward kernels it overlaps with
+  const size_t cap = static_cast<size_t>(sms) * 2;  // 1024 threads/SM: leaves room for the backward kernels it overlaps with
   if (blocks > cap) blocks = cap;
   if (blocks == 0) blocks = 1;
   return static_cast<int>(blocks);

@@ -292,7 +292,7 @@ def run_b200(args) -> dict:
     timed(max(args.warmup, 3), e2e=False, first_step=0)
 
     sampler = ClockSampler(local_rank)
-    if rank == 0:
+    if rank == 0 and not args.no_clocks:
         sampler.start()
     ops.STATS.reset(with_events=True)
     ms_step, wall_dev, _ = timed(args.steps, e2e=False, first_step=100)
@@ -482,6 +482,7 @@ def main():
     ap.add_argument("--cpu-tokens", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")
+    ap.add_argument("--no-clocks", action="store_true", help="profiling runs only: do not spawn the nvidia-smi sampler")
     ap.add_argument("--kernel-table", default=None, metavar="PATH",
                     help="after the timed passes, trace ONE more step with torch.profiler (CUPTI) and write the "
                          "per-kernel device-time table (markdown) to PATH")

@@ -40,6 +40,10 @@ extern "C" {
 
 const char* b200sft_last_error(void);
 int b200sft_version(void);
+/* Process-wide tile configuration of the tcgen05 GEMM engine: 1 = one CTA per 128x256 tile
+ * (tcgen05.mma.cta_group::1), 2 = two-CTA clusters on 256x256 tiles (cta_group::2, operands split
+ * across the SM pair; the default).  Results are identical; no reference counterpart. */
+int b200sft_set_cta_group(int cta_group);
 
 /* ---------------------------------------------------------------------------------------------
  * Label front-end.  Replaces the shift in ForCausalLMLoss (SP/transformers/loss/loss_utils.py:57-60:

@@ -6,6 +6,7 @@ library is missing or a call fails, the caller gets an exception.
 from __future__ import annotations
 
 import ctypes
+import os
 from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_uint32, c_void_p
 from pathlib import Path
 
@@ -19,6 +20,7 @@ NOALLOC_SCRATCH_BYTES = 40 << 20  # B200SFT_NOALLOC_SCRATCH_BYTES
 SIGNATURES = {
     "b200sft_last_error": (c_char_p, []),
     "b200sft_version": (c_int, []),
+    "b200sft_set_cta_group": (c_int, [c_int]),
     "b200sft_label_prep": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_void_p]),
     "b200sft_flce_fwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "b200sft_flce_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
@@ -70,7 +72,15 @@ def load() -> ctypes.CDLL:
         fn.restype = restype
         fn.argtypes = argtypes
     _lib = lib
+    grp = os.environ.get("B200SFT_CTA_GROUP")
+    if grp:
+        check(lib.b200sft_set_cta_group(int(grp)), "b200sft_set_cta_group")
     return lib
+
+
+def set_cta_group(cta_group: int) -> None:
+    """1 = one CTA per 128x256 tile, 2 = two-CTA clusters on 256x256 tiles (process-wide)."""
+    check(load().b200sft_set_cta_group(int(cta_group)), "b200sft_set_cta_group")
 
 
 def check(rc: int, what: str) -> None:

@@ -524,36 +524,64 @@ int num_sms() {
   return sms[dev] > 0 ? sms[dev] : 148;
 }
 
-// Rasterisation group for the M-fastest (logit) GEMMs: 64 tiles = 8192 rows of X (33.5 MB at
+// Rasterisation group for the M-fastest (logit) GEMMs: 8192 rows of X (33.5 MB at
 // H = 2048) stay L2-resident while every vocabulary tile is swept over them; W is re-streamed
 // once per group.  Without it N = 65536 re-reads all of X from HBM for each of the 501 W panels.
-constexpr int GROUP_M_TILES = 64;
+constexpr int GROUP_M_ROWS = 8192;
+
+// 1 = one CTA per 128x256 tile (cta_group::1); 2 = CTA pairs on 256x256 tiles (cta_group::2).
+// Default 2: measured 5-6 % faster on the backward GEMMs and 4 % on the forward at N = 65536
+// (profiles/r01_cta_pair_vs_single.log); results are bit-identical.
+int g_cta_group = 2;
 
 template <class Epi, bool A_MN, bool B_MN>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
                 const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
+  const bool paired = (g_cta_group == 2);
   CUtensorMap ta, tb;
   int rc = make_operand_tmap(&ta, a, M, K, lda, A_MN, BLOCK_M);
   if (rc != 0) return rc;
-  rc = make_operand_tmap(&tb, b, N, K, ldb, B_MN, BLOCK_N);
+  rc = make_operand_tmap(&tb, b, N, K, ldb, B_MN, paired ? pair::B_ROWS_PER_CTA : BLOCK_N);
   if (rc != 0) return rc;
+  const int tile_m = paired ? pair::TILE_M : BLOCK_M;
   GemmShape s;
   s.M = M;
   s.N = N;
   s.K = K;
-  s.tiles_m = (M + BLOCK_M - 1) / BLOCK_M;
+  s.tiles_m = (M + tile_m - 1) / tile_m;
   s.tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
   s.m_fastest = m_fastest;
-  s.group_m = s.tiles_m < GROUP_M_TILES ? s.tiles_m : GROUP_M_TILES;
+  const int group = GROUP_M_ROWS / tile_m;
+  s.group_m = s.tiles_m < group ? s.tiles_m : group;
   s.dyn_rows = dyn_rows;
   s.dyn_is_k = dyn_is_k;
-  auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
-  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
-  const int grid = static_cast<int>(tiles < num_sms() ? tiles : num_sms());
-  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(ta, tb, s, ep);
-  B200_CUDA_CHECK(cudaGetLastError());
+  if (!paired) {
+    auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    const int grid = static_cast<int>(tiles < num_sms() ? tiles : num_sms());
+    kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(ta, tb, s, ep);
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200SFT_OK;
+  }
+  auto kern = gemm_tcgen05_2cta_kernel<Epi, A_MN, B_MN>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::SMEM_BYTES));
+  const int max_pairs = num_sms() / 2;
+  const int pairs = static_cast<int>(tiles < max_pairs ? tiles : max_pairs);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = pair::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, s, ep));
   return B200SFT_OK;
 }
 
@@ -825,6 +853,12 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, n_rows_dev, 1);
     if (rc != 0) return rc;
   }
+  return B200SFT_OK;
+}
+
+int b200sft_set_cta_group(int cta_group) {
+  if (cta_group != 1 && cta_group != 2) return fail(B200SFT_ERR_INVALID, "cta_group must be 1 or 2 (got %d)", cta_group);
+  g_cta_group = cta_group;
   return B200SFT_OK;
 }
 

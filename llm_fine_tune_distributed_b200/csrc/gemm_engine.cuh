@@ -250,4 +250,217 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   }
 }
 
+
+// =============================================================================================
+// cta_group::2 variant: a cluster of two CTAs (an SM pair) works on one 256 x 256 output tile.
+//
+// Each CTA streams its own 128 rows of A and its own half (128 rows) of B -- 32 KiB per k-block
+// instead of 48, so the ring is 6 deep -- and the leader CTA's MMA thread issues
+// tcgen05.mma.cta_group::2 (M = 256), which reads A and B from both CTAs' shared memory and
+// accumulates 128 rows in each CTA's TMEM.  TMA completions of both CTAs are credited to the
+// leader's "full" barrier; tcgen05.commit multicasts to both CTAs' "empty" / "accumulator full"
+// barriers; both CTAs' epilogue warps arrive on the leader's "accumulator empty" barrier.
+// Same epilogue functors; TileCoord::m0 is this CTA's first row.
+// =============================================================================================
+namespace pair {
+
+constexpr int TILE_M = 2 * BLOCK_M;                    // 256 rows per CTA pair
+constexpr int B_ROWS_PER_CTA = BLOCK_N / 2;            // 128 rows of B per CTA
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;         // 16 KiB
+constexpr int B_BYTES = B_ROWS_PER_CTA * BLOCK_K * 2;  // 16 KiB
+constexpr int CTA_STAGE_BYTES = A_BYTES + B_BYTES;     // 32 KiB per CTA per stage
+constexpr int STAGES = 6;
+constexpr int SMEM_BYTES = STAGES * CTA_STAGE_BYTES + EPI_SMEM_BYTES + 1024 + SMEM_BARRIER_BYTES;
+
+__device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile, int cta_rank) {
+  TileCoord c;  // s.tiles_m / s.group_m count 256-row tiles here
+  if (s.m_fastest) {
+    const int per_group = s.group_m * s.tiles_n;
+    const int g = tile / per_group;
+    const int r = tile - g * per_group;
+    const int left = s.tiles_m - g * s.group_m;
+    const int gm = left < s.group_m ? left : s.group_m;
+    c.tile_m = g * s.group_m + r % gm;
+    c.tile_n = r / gm;
+  } else {
+    c.tile_n = tile % s.tiles_n;
+    c.tile_m = tile / s.tiles_n;
+  }
+  c.m0 = c.tile_m * TILE_M + cta_rank * BLOCK_M;
+  c.n0 = c.tile_n * BLOCK_N;
+  return c;
+}
+
+}  // namespace pair
+
+template <class Epi, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                             const GemmShape shape_in, const __grid_constant__ typename Epi::Params epi_params) {
+  using namespace pair;
+  GemmShape shape = shape_in;  // tiles_m / group_m arrive in units of 256-row tiles
+  if (shape.dyn_rows != nullptr) {
+    int r = __ldg(shape.dyn_rows);
+    if (shape.dyn_is_k) {
+      shape.K = r < shape.K ? (r < 0 ? 0 : r) : shape.K;
+    } else {
+      shape.M = r < shape.M ? (r < 0 ? 0 : r) : shape.M;
+      shape.tiles_m = (shape.M + TILE_M - 1) / TILE_M;
+      if (shape.group_m > shape.tiles_m) shape.group_m = shape.tiles_m > 0 ? shape.tiles_m : 1;
+    }
+  }
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_BYTES;
+  uint8_t* smem_epi = smem + STAGES * CTA_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * CTA_STAGE_BYTES + EPI_SMEM_BYTES);
+  uint64_t* full_bar = bars;                                  // [STAGES]  used in the leader CTA
+  uint64_t* empty_bar = bars + STAGES;                        // [STAGES]  per CTA (multicast commit)
+  uint64_t* acc_full_bar = bars + 2 * STAGES;                 // [2]       per CTA (multicast commit)
+  uint64_t* acc_empty_bar = bars + 2 * STAGES + NUM_ACC_STAGES;  // [2]    used in the leader CTA
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2 * NUM_ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int cta_rank = static_cast<int>(cluster_ctarank());
+  const int pair_id = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int num_tiles = shape.tiles_m * shape.tiles_n;
+  const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < NUM_ACC_STAGES; ++i) {
+      mbar_init(&acc_full_bar[i], 1);
+      mbar_init(&acc_empty_bar[i], 2 * NUM_EPI_WARPS);  // epilogue warps of both CTAs
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<2>(tmem_ptr_smem, TMEM_COLS);
+  tc_fence_before_sync();
+  cluster_sync_all();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ------------------------------- TMA producer (both CTAs) -------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+        const TileCoord tc = tile_coord(shape, tile, cta_rank);
+        const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * CTA_STAGE_BYTES);  // both CTAs' bytes
+          uint8_t* sa = smem_a + stage * A_BYTES;
+          uint8_t* sb = smem_b + stage * B_BYTES;
+          const int k0 = kb * BLOCK_K;
+          if constexpr (!A_MN) {
+            tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, tc.m0);  // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / 64; ++j)
+              tma_load_2d_pair(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, b_row0);  // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < B_ROWS_PER_CTA / 64; ++j)
+              tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), b_row0 + j * 64, k0);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------- MMA issuer (leader CTA only) -------------------------------
+    if (cta_rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t A_LBO = A_MN ? BLOCK_K * 128 : 16, B_LBO = B_MN ? BLOCK_K * 128 : 16;
+      constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(&acc_empty_bar[as], aphase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(smem_a + stage * A_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + stage * B_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+            const uint64_t da = make_smem_desc_sw128(a_addr + kk * A_KSTEP, A_LBO, 1024);
+            const uint64_t db = make_smem_desc_sw128(b_addr + kk * B_KSTEP, B_LBO, 1024);
+            umma_bf16<2>(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit<2>(&empty_bar[stage], 0x3);  // frees the stage in both CTAs
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit<2>(&acc_full_bar[as], 0x3);  // accumulator halves complete in both CTAs
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------- epilogue warps (both CTAs) -------------------------------
+    const int quarter = warp & 3;
+    const int row_in_tile = quarter * 32 + lane;  // row within this CTA's 128-row half
+    Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
+    int it = 0;
+    for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+      const TileCoord tc = tile_coord(shape, tile, cta_rank);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      epi.tile_begin(tc, row_in_tile);
+      mbar_wait(&acc_full_bar[as], aphase);
+      tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t acc[32];
+        __syncwarp();
+        if (num_kb > 0) {
+          tmem_ld_32x32b_x32(taddr + c, acc);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[j] = 0u;
+        }
+        epi.chunk(tc, row_in_tile, c, acc);
+      }
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&acc_empty_bar[as], 0);  // the leader's barrier
+      epi.tile_end(tc, row_in_tile);
+    }
+    epi.finish();
+  }
+
+  tc_fence_before_sync();
+  cluster_sync_all();  // neither CTA may exit (or free TMEM) while its peer can still touch its smem / barriers
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc<2>(tmem_base, TMEM_COLS);
+  }
+}
+
 }  // namespace b200

@@ -1,0 +1,69 @@
+"""The driver with the reference's surface (`python -m llm_fine_tune_distributed_b200.training`,
+configured only through the reference's environment variables) runs BASELINE config 1 -- tiny
+random-init SmolLM3 (2 layers, hidden 256, vocab 128,256) on a QA parquet file -- on one GPU through
+the fused kernels, and writes the artefacts training.py:309-335 writes."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _write_parquet(path, n=96):
+    import pandas as pd
+
+    pd.DataFrame({
+        "full-question": [f"For topic {i % 7}, what should I do in situation {i}?" for i in range(n)],
+        "answer": [("Check your surroundings, stay calm, and act deliberately. " * (i % 5 + 1)).strip() for i in range(n)],
+    }).to_parquet(path, compression="snappy")
+
+
+def _env(tmp_path, **extra):
+    env = dict(os.environ)
+    env.update(RANDOM_INIT="1", MODEL_CONFIG="tiny", ATTN_IMPL="sdpa", MAX_STEPS="3", BATCH_SIZE="4", GRAD_ACCUM="2",
+               EPOCHS="1", LEARNING_RATE="1e-4", DATASET_PATH=str(tmp_path / "qa.parquet"),
+               OUTPUT_DIR=str(tmp_path / "out"), PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
+    env.update(extra)
+    return env
+
+
+def _check(tmp_path, world):
+    out = tmp_path / "out"
+    summary = json.load(open(out / "training_summary.json"))
+    history = json.load(open(out / "training_history.json"))
+    assert summary["world_size"] == world and summary["distributed_training"] == (world > 1)
+    assert summary["training_samples"] + summary["validation_samples"] == 96
+    assert summary["trainable_params"] <= summary["total_params"]
+    # logging_first_step=True, logging_steps=2 (training.py:266-267): 3 optimizer steps log at steps 1 and 2
+    assert len(history) == 2 and all(8.0 < h["loss"] < 16.0 and "perplexity" in h for h in history)
+    assert os.path.isdir(out / "best_model") and os.listdir(out / "best_model")
+
+
+def test_driver_single_gpu(cuda_device, tmp_path):
+    _write_parquet(tmp_path / "qa.parquet")
+    res = subprocess.run([sys.executable, "-m", "llm_fine_tune_distributed_b200.training"], cwd=ROOT,
+                         env=_env(tmp_path, WORLD_SIZE="1", RANK="0", LOCAL_RANK="0"), capture_output=True, text=True,
+                         timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    _check(tmp_path, 1)
+
+
+def test_driver_two_gpus_ddp(cuda_device, tmp_path):
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    _write_parquet(tmp_path / "qa.parquet")
+    env = _env(tmp_path)
+    for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
+        env.pop(k, None)
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29761", "-m",
+                          "llm_fine_tune_distributed_b200.training"], cwd=ROOT, env=env, capture_output=True, text=True,
+                         timeout=400)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    _check(tmp_path, 2)

@@ -227,7 +227,12 @@ def run_b200(args) -> dict:
             wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
         wrapped._b200sft_hook = True
     params = [p for p in model.parameters() if p.requires_grad]
-    opt = torch.optim.AdamW(params, lr=5e-5 * world, weight_decay=0.0, fused=True)
+    if args.tail == "b200":
+        from llm_fine_tune_distributed_b200.optim import B200AdamW
+
+        opt = B200AdamW(params, lr=5e-5 * world, weight_decay=0.0)
+    else:
+        opt = torch.optim.AdamW(params, lr=5e-5 * world, weight_decay=0.0, fused=True)
 
     class Seam(FusedCELossMixin):
         num_processes = world
@@ -249,8 +254,11 @@ def run_b200(args) -> dict:
                 loss = seam.compute_loss(wrapped, dict(mb), num_items_in_batch=n_items)
                 loss.backward()
             total_loss += loss.detach()
-        torch.nn.utils.clip_grad_norm_(params, 1.0)
-        opt.step()
+        if args.tail == "b200":
+            opt.clip_and_step(1.0)          # grad-norm + clip + AdamW in this library's multi-tensor kernels
+        else:
+            torch.nn.utils.clip_grad_norm_(params, 1.0)
+            opt.step()
         opt.zero_grad(set_to_none=True)
         return total_loss
 
@@ -355,7 +363,7 @@ def run_b200(args) -> dict:
         "config": {
             "workload": f"SmolLM3-3B random-init bf16 SFT optimizer step: seq {T}, per-device batch {B}, grad-accum {GA}, "
                         "freeze policy last-2-layers+tied lm_head, gradient checkpointing, fused LM-head+CE (sm_100a), "
-                        "clip 1.0, fused AdamW" + (f", DDP bucket 50 MiB + b200 comm hook ({args.comm})" if world > 1 else ""),
+                        f"clip 1.0 + AdamW ({args.tail} kernels)" + (f", DDP bucket 50 MiB + b200 comm hook ({args.comm})" if world > 1 else ""),
             "global_batch": B * GA * world, "seq_len": T, "parallelism": f"dp{world}", "attn": attn,
             "rows": {"full": "full-length rows, every position trains",
                      "padded": "variable-length rows right-padded to seq_len (reference collator), -100 on padding",
@@ -474,6 +482,8 @@ def main():
     ap.add_argument("--ga", type=int, default=2)
     ap.add_argument("--layers", type=int, default=None, help="debug only: fewer decoder layers (invalid as a result)")
     ap.add_argument("--attn", default="auto")
+    ap.add_argument("--tail", default="b200", choices=["b200", "torch"],
+                    help="step tail: this library's fused grad-norm clip + AdamW kernels, or torch's clip_grad_norm_ + fused AdamW")
     ap.add_argument("--comm", default="nccl", choices=["nccl", "nvlink"],
                     help="N>1: gradient hook = scale kernel + NCCL allreduce (default), or this library's fused "
                          "NVLink reduce+scale kernel over symmetric memory")

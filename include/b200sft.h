@@ -204,6 +204,24 @@ int b200sft_allreduce_scale_bf16_multimem(void* multicast_ptr, size_t n, int ran
 int b200sft_allreduce_scale_bf16_p2p(const uint64_t* peer_ptrs_host, size_t n, int rank, int world, float scale,
                                      void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Step tail on bf16 parameters: global gradient-norm clip + AdamW as two multi-tensor kernels.
+ * Replaces accelerator.clip_grad_norm_(params, max_grad_norm=1.0) (training.py:264 ->
+ * SP/transformers/trainer.py:2489-2499 -> torch.nn.utils.clip_grad_norm_) and torch.optim.AdamW.step on
+ * the trainable tensors.  The pointer arrays are HOST arrays of n_tensors device pointers.
+ *   grad_norm : total_norm (fp32 device scalar) = sqrt(sum g^2) over all tensors, fixed summation order
+ *   adamw     : g = bf16(grad * min(1, max_norm / (total_norm + 1e-6)))  (max_norm <= 0: no clipping),
+ *               then torch's AdamW update in fp32 with one bf16 rounding per stored value; `step`
+ *               counts from 1.  Gradients are not modified.
+ */
+size_t b200sft_grad_norm_workspace_bytes(const size_t* numels, int n_tensors);
+int b200sft_grad_norm_bf16(void* const* grads, const size_t* numels, int n_tensors, float* total_norm,
+                           void* workspace, size_t workspace_bytes, void* stream);
+int b200sft_adamw_clip_bf16(void* const* params, void* const* grads, void* const* exp_avgs,
+                            void* const* exp_avg_sqs, const size_t* numels, int n_tensors, float lr, float beta1,
+                            float beta2, float eps, float weight_decay, int step, float max_norm,
+                            const float* total_norm, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

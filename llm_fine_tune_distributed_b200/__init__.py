@@ -5,7 +5,7 @@ and the DDP gradient-bucket hook, behind the reference's own seams
 
 Layout:  csrc/ (CUDA kernels + C ABI, built into libb200sft.so), _cabi.py (ctypes binding),
 ops.py (torch custom ops), loss.py (compute_loss seam), comm_hook.py (DDP hook seam),
-training.py (driver with the reference's env/SFTConfig surface).
+optim.py (grad-norm clip + AdamW step tail), training.py (driver with the reference's env/SFTConfig surface).
 """
 from . import _cabi  # noqa: F401
 from .ops import (  # noqa: F401
@@ -22,5 +22,7 @@ from .ops import (  # noqa: F401
 )
 from .loss import FusedCELossMixin, FusedLMHead, fused_causal_lm_loss, fused_head_armed, install_fused_head  # noqa: F401
 from .comm_hook import B200HookState, b200_allreduce_hook, b200_bf16_compress_hook, register_b200_comm_hook  # noqa: F401
+
+from .optim import B200AdamW  # noqa: F401
 
 __version__ = "0.1.0"

@@ -45,6 +45,10 @@ SIGNATURES = {
     "b200sft_scale_f32_inplace": (c_int, [c_void_p, c_size_t, c_float, c_void_p]),
     "b200sft_scale_cast_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_size_t, c_float, c_void_p]),
     "b200sft_cast_bf16_to_f32": (c_int, [c_void_p, c_void_p, c_size_t, c_float, c_void_p]),
+    "b200sft_grad_norm_workspace_bytes": (c_size_t, [c_void_p, c_int]),
+    "b200sft_grad_norm_bf16": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200sft_adamw_clip_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_float,
+                                        c_float, c_float, c_float, c_int, c_float, c_void_p, c_void_p]),
     "b200sft_allreduce_scale_bf16_multimem": (c_int, [c_void_p, c_size_t, c_int, c_int, c_float, c_void_p]),
     "b200sft_allreduce_scale_bf16_p2p": (c_int, [c_void_p, c_size_t, c_int, c_int, c_float, c_void_p]),
 }

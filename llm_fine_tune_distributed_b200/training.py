@@ -285,8 +285,13 @@ class MiniSFTTrainer(FusedCELossMixin):
                 self.model_wrapped._b200sft_hook = True
         self.train_batches, self.eval_batches = train_batches, eval_batches
         params = [p for p in self.model.parameters() if p.requires_grad]
-        fused = self.device.type == "cuda"
-        self.optimizer = torch.optim.AdamW(params, lr=args.learning_rate, weight_decay=args.weight_decay, fused=fused)
+        self.fused_tail = self.device.type == "cuda" and all(p.dtype == torch.bfloat16 for p in params)
+        if self.fused_tail:  # grad-norm clip + AdamW in this library's multi-tensor kernels
+            from .optim import B200AdamW
+
+            self.optimizer = B200AdamW(params, lr=args.learning_rate, weight_decay=args.weight_decay)
+        else:                # CPU plumbing runs (gloo) and non-bf16 models: torch's own step tail
+            self.optimizer = torch.optim.AdamW(params, lr=args.learning_rate, weight_decay=args.weight_decay)
         steps_per_epoch = max(len(train_batches) // args.gradient_accumulation_steps, 1)
         self.max_steps = args.max_steps if args.max_steps > 0 else int(math.ceil(args.num_train_epochs * steps_per_epoch))
         self.lr_scheduler = torch.optim.lr_scheduler.LambdaLR(
@@ -348,9 +353,12 @@ class MiniSFTTrainer(FusedCELossMixin):
                     with ctx:  # trainer.py:1725-1733 -> DDP.no_sync
                         tr_loss += self.training_step(inputs, num_items)
                     tokens_seen += int(inputs["attention_mask"].sum())
-                grad_norm = torch.nn.utils.clip_grad_norm_(
-                    [p for p in self.model.parameters() if p.requires_grad], args.max_grad_norm)
-                self.optimizer.step()
+                if self.fused_tail:
+                    grad_norm = self.optimizer.clip_and_step(args.max_grad_norm)
+                else:
+                    grad_norm = torch.nn.utils.clip_grad_norm_(
+                        [p for p in self.model.parameters() if p.requires_grad], args.max_grad_norm)
+                    self.optimizer.step()
                 self.lr_scheduler.step()
                 self.optimizer.zero_grad(set_to_none=True)
                 self.global_step += 1

@@ -66,6 +66,7 @@ class B200AdamW(torch.optim.Optimizer):
     def clip_and_step(self, max_norm: Optional[float] = None) -> Optional[torch.Tensor]:
         total = self.grad_norm() if (max_norm is not None and max_norm > 0) else None
         self._t += 1
+        self._opt_called = True  # lets torch LR schedulers see that an optimizer step happened
         lib = _cabi.load()
         for group in self.param_groups:
             ps = self._tensors(group)

@@ -1,0 +1,57 @@
+"""BASELINE.json's full head size (8192 tokens x hidden 2048 x vocabulary 128,256, 60 % of the rows
+masked as completion-only SFT would): parity with the oracle run on the same GPU, plus
+size-independent properties of the gradients."""
+import pytest
+import torch
+
+from oracle import sft_oracle as oracle
+
+pytestmark = pytest.mark.gpu
+N, H, V = 8192, 2048, 128256
+
+
+@pytest.fixture(scope="module")
+def case(cuda_device):
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(N, H, generator=g).to(torch.bfloat16).to(cuda_device)
+    w = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(torch.bfloat16).to(cuda_device)
+    labels = torch.randint(0, V, (N,), generator=torch.Generator().manual_seed(2))
+    labels.view(8, 1024)[:, :614] = -100          # first 60 % of every 1024-token row is prompt
+    return x, w, labels.to(cuda_device)
+
+
+def _cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a @ b) / (a.norm() * b.norm()))
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_full_size_parity_and_properties(cuda_device, case, skip):
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = case
+    n_items = torch.tensor(int((labels != -100).sum()) + 17, dtype=torch.int64, device=cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    loss = ops.fused_linear_cross_entropy(xg, wg, labels.to(torch.int32), n_items, skip_ignored_rows=skip)
+    loss.backward()
+    ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, float(n_items))
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
+    cdx, cdw = _cos(xg.grad, ref_dx), _cos(wg.grad, ref_dw)
+    rel_dx = float((xg.grad.float() - ref_dx.float()).abs().max() / ref_dx.float().abs().max())
+    rel_dw = float((wg.grad.float() - ref_dw.float()).abs().max() / ref_dw.float().abs().max())
+    print(f"full size: loss {loss.item():.6f} vs {ref_loss.item():.6f}; cos dx {cdx:.6f} dw {cdw:.6f}; "
+          f"max-rel-err dx {rel_dx:.3e} dw {rel_dw:.3e}")
+    assert cdx >= 0.999 and cdw >= 0.999
+    assert rel_dx <= 2e-2 and rel_dw <= 2e-2
+
+    ign = labels == -100
+    assert torch.count_nonzero(xg.grad[ign]) == 0                       # ignored rows get exactly zero dX
+    # every dlogits row sums to zero (softmax - onehot), hence sum_v dW[v, :] = 0 up to bf16 rounding of dW
+    col_sum = wg.grad.float().sum(dim=0).abs().max()
+    assert float(col_sum) <= 64 * 2.0 ** -8 * float(wg.grad.float().abs().max()) * 8
+
+    # linearity in the upstream gradient: a power-of-two scale commutes with every rounding
+    xg2, wg2 = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    (ops.fused_linear_cross_entropy(xg2, wg2, labels.to(torch.int32), n_items, skip_ignored_rows=skip) * 4.0).backward()
+    assert torch.equal(xg2.grad, xg.grad * 4) and torch.equal(wg2.grad, wg.grad * 4)

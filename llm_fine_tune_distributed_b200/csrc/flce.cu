@@ -534,15 +534,17 @@ constexpr int GROUP_M_ROWS = 8192;
 // (profiles/r01_cta_pair_vs_single.log); results are bit-identical.
 int g_cta_group = 2;
 
-template <class Epi, bool A_MN, bool B_MN>
+// BN = output tile width of the pair engine (256; 128 is implemented and tested but slower, see DX_TILE_N).
+template <class Epi, bool A_MN, bool B_MN, int BN = 256>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
                 const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
   const bool paired = (g_cta_group == 2);
+  const int bn = paired ? BN : BLOCK_N;  // the single-CTA engine has one tile shape
   CUtensorMap ta, tb;
   int rc = make_operand_tmap(&ta, a, M, K, lda, A_MN, BLOCK_M);
   if (rc != 0) return rc;
-  rc = make_operand_tmap(&tb, b, N, K, ldb, B_MN, paired ? pair::B_ROWS_PER_CTA : BLOCK_N);
+  rc = make_operand_tmap(&tb, b, N, K, ldb, B_MN, paired ? bn / 2 : BLOCK_N);
   if (rc != 0) return rc;
   const int tile_m = paired ? pair::TILE_M : BLOCK_M;
   GemmShape s;
@@ -550,7 +552,7 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.N = N;
   s.K = K;
   s.tiles_m = (M + tile_m - 1) / tile_m;
-  s.tiles_n = (N + BLOCK_N - 1) / BLOCK_N;
+  s.tiles_n = (N + bn - 1) / bn;
   s.m_fastest = m_fastest;
   const int group = GROUP_M_ROWS / tile_m;
   s.group_m = s.tiles_m < group ? s.tiles_m : group;
@@ -565,14 +567,15 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
     B200_CUDA_CHECK(cudaGetLastError());
     return B200SFT_OK;
   }
-  auto kern = gemm_tcgen05_2cta_kernel<Epi, A_MN, B_MN>;
-  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::SMEM_BYTES));
+  auto kern = gemm_tcgen05_2cta_kernel<Epi, A_MN, B_MN, BN>;
+  constexpr int smem_bytes = pair::Cfg<BN>::SMEM_BYTES;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int max_pairs = num_sms() / 2;
   const int pairs = static_cast<int>(tiles < max_pairs ? tiles : max_pairs);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(GEMM_THREADS);
-  cfg.dynamicSmemBytes = pair::SMEM_BYTES;
+  cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -590,6 +593,10 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // Backward stages dlogits one vocabulary slab at a time: [N][slab_cols] bf16.  The default slab
 // width keeps that scratch within ~1 GiB and splits V into equal slabs (multiples of 256 columns).
 constexpr size_t DEFAULT_DLOGITS_SCRATCH_BYTES = size_t(1) << 30;
+// dX = dlogits . W has few tiles with a very long K (32 x 8 tiles on 74 CTA pairs = 3.46 waves).  128-wide
+// tiles would make it 6.92 waves, but measured 10.9 ms instead of 8.9 ms for the whole backward at
+// N = 8192: operand traffic per flop rises 1.5x and the L2->SM path saturates.  So: 256.
+constexpr int DX_TILE_N = 256;
 
 int resolve_slab_cols(int N, int V, int chunk_cols) {
   const int v_up = (V + BLOCK_N - 1) / BLOCK_N * BLOCK_N;
@@ -839,7 +846,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
       sx.mode = ACCUM_F32_OUT_BF16;
     else
       sx.mode = ACCUM_F32;
-    rc = launch_gemm<StoreEpi, false, true>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream, n_rows_dev, 0);
+    rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream,
+                                                       n_rows_dev, 0);
     if (rc != 0) return rc;
 
     // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every

@@ -264,14 +264,23 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 // =============================================================================================
 namespace pair {
 
-constexpr int TILE_M = 2 * BLOCK_M;                    // 256 rows per CTA pair
-constexpr int B_ROWS_PER_CTA = BLOCK_N / 2;            // 128 rows of B per CTA
-constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;         // 16 KiB
-constexpr int B_BYTES = B_ROWS_PER_CTA * BLOCK_K * 2;  // 16 KiB
-constexpr int CTA_STAGE_BYTES = A_BYTES + B_BYTES;     // 32 KiB per CTA per stage
-constexpr int STAGES = 6;
-constexpr int SMEM_BYTES = STAGES * CTA_STAGE_BYTES + EPI_SMEM_BYTES + 1024 + SMEM_BARRIER_BYTES;
+constexpr int TILE_M = 2 * BLOCK_M;             // 256 rows per CTA pair
+constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
 
+// Tile width BN = 256 (used everywhere) or 128 (kept for experiments: it halves wave quantisation for
+// GEMMs with few long tiles, but costs 1.5x the operand traffic per flop and measured slower).
+template <int BN>
+struct Cfg {
+  static_assert(BN == 256 || BN == 128, "pair tile width");
+  static constexpr int B_ROWS_PER_CTA = BN / 2;
+  static constexpr int B_BYTES = B_ROWS_PER_CTA * BLOCK_K * 2;
+  static constexpr int CTA_STAGE_BYTES = A_BYTES + B_BYTES;  // 32 / 24 KiB per CTA per stage
+  static constexpr int STAGES = (BN == 256) ? 6 : 8;
+  static constexpr int TMEM_COLS = NUM_ACC_STAGES * BN;       // 512 / 256
+  static constexpr int SMEM_BYTES = STAGES * CTA_STAGE_BYTES + EPI_SMEM_BYTES + 1024 + SMEM_BARRIER_BYTES;
+};
+
+template <int BN>
 __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile, int cta_rank) {
   TileCoord c;  // s.tiles_m / s.group_m count 256-row tiles here
   if (s.m_fastest) {
@@ -287,17 +296,20 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile, in
     c.tile_m = tile / s.tiles_n;
   }
   c.m0 = c.tile_m * TILE_M + cta_rank * BLOCK_M;
-  c.n0 = c.tile_n * BLOCK_N;
+  c.n0 = c.tile_n * BN;
   return c;
 }
 
 }  // namespace pair
 
-template <class Epi, bool A_MN, bool B_MN>
+template <class Epi, bool A_MN, bool B_MN, int BN = 256>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
     gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                              const GemmShape shape_in, const __grid_constant__ typename Epi::Params epi_params) {
   using namespace pair;
+  using C = Cfg<BN>;
+  constexpr int STAGES = C::STAGES, B_BYTES = C::B_BYTES, CTA_STAGE_BYTES = C::CTA_STAGE_BYTES,
+                B_ROWS_PER_CTA = C::B_ROWS_PER_CTA, TMEM_COLS = C::TMEM_COLS;
   GemmShape shape = shape_in;  // tiles_m / group_m arrive in units of 256-row tiles
   if (shape.dyn_rows != nullptr) {
     int r = __ldg(shape.dyn_rows);
@@ -354,7 +366,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
-        const TileCoord tc = tile_coord(shape, tile, cta_rank);
+        const TileCoord tc = tile_coord<BN>(shape, tile, cta_rank);
         const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -387,7 +399,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   } else if (warp == 1) {
     // ------------------------------- MMA issuer (leader CTA only) -------------------------------
     if (cta_rank == 0 && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       constexpr uint32_t A_LBO = A_MN ? BLOCK_K * 128 : 16, B_LBO = B_MN ? BLOCK_K * 128 : 16;
       constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
       int stage = 0;
@@ -398,7 +410,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
         tc_fence_after_sync();
-        const uint32_t d_tmem = tmem_base + as * BLOCK_N;
+        const uint32_t d_tmem = tmem_base + as * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
@@ -427,15 +439,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
-      const TileCoord tc = tile_coord(shape, tile, cta_rank);
+      const TileCoord tc = tile_coord<BN>(shape, tile, cta_rank);
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       epi.tile_begin(tc, row_in_tile);
       mbar_wait(&acc_full_bar[as], aphase);
       tc_fence_after_sync();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BLOCK_N;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
+      for (int c = 0; c < BN; c += 32) {
         uint32_t acc[32];
         __syncwarp();
         if (num_kb > 0) {

@@ -231,3 +231,22 @@ def test_flce_token_stats_vs_oracle(cuda_device, N, H, V, masked, skip):
     assert abs(float(stats["entropy_sum"]) - ent) <= 1e-3 * abs(ent) + 1e-3
     ref = oracle.lm_head_ce(x, w, labels, None)
     assert abs(loss.item() - ref.item()) <= 1e-3 * abs(ref.item())
+
+
+def test_flce_is_bitwise_deterministic(cuda_device):
+    """No atomics on floating-point data anywhere in the path: two runs give identical bits."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = _case(1536, 256, 8192, 0.4, seed=99, device=cuda_device)
+    lab = labels.to(torch.int32)
+    denom = torch.tensor(int((labels != -100).sum()), dtype=torch.int64, device=cuda_device)
+    runs = []
+    for _ in range(2):
+        for skip in (False, True):
+            xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+            loss = ops.fused_linear_cross_entropy(xg, wg, lab, denom, skip_ignored_rows=skip, chunk_cols=2048)
+            loss.backward()
+            runs.append((skip, loss.detach().clone(), xg.grad.clone(), wg.grad.clone()))
+    torch.cuda.synchronize()
+    for (s0, l0, dx0, dw0), (s1, l1, dx1, dw1) in ((runs[0], runs[2]), (runs[1], runs[3])):
+        assert s0 == s1 and torch.equal(l0, l1) and torch.equal(dx0, dx1) and torch.equal(dw0, dw1)

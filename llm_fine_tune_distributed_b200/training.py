@@ -97,6 +97,7 @@ class SFTSettings:
             gradient_accumulation_steps=int(os.getenv("GRAD_ACCUM", "4")),
             ddp_backend="nccl" if world_size > 1 else None,
             local_rank=local_rank,
+            packing=os.getenv("PACKING", "0") == "1",  # reference: False (training.py:283); 1 = padding-free batches
         )
 
 
@@ -169,16 +170,23 @@ class ByteChatTokenizer:
     def __init__(self, vocab_size: int = 128256):
         self.vocab_size = vocab_size
 
-    def apply_chat_template(self, messages: List[Dict[str, str]]) -> List[int]:
+    def apply_chat_template(self, messages: List[Dict[str, str]], return_assistant_mask: bool = False):
+        """Token ids of the templated conversation; with ``return_assistant_mask`` also a 0/1 list
+        marking the assistant's tokens (what TRL's ``assistant_only_loss`` trains on)."""
         ids: List[int] = []
+        mask: List[int] = []
         for m in messages:
-            text = f"<|im_start|>{m['role']}\n{m['content']}<|im_end|>\n"
-            ids.extend(2 + (b % (self.vocab_size - 2)) for b in text.encode("utf-8"))
+            head = f"<|im_start|>{m['role']}\n".encode("utf-8")
+            body = f"{m['content']}<|im_end|>\n".encode("utf-8")
+            ids.extend(2 + (b % (self.vocab_size - 2)) for b in head + body)
+            mask.extend([0] * len(head) + [1 if m["role"] == "assistant" else 0] * len(body))
         ids.append(self.eos_token_id)
-        return ids
+        mask.append(1)
+        return (ids, mask) if return_assistant_mask else ids
 
 
-def collate(samples: List[List[int]], pad_id: int, max_len: int, pad_to: Optional[int] = None) -> Dict[str, torch.Tensor]:
+def collate(samples: List[List[int]], pad_id: int, max_len: int, pad_to: Optional[int] = None,
+            masks: Optional[List[List[int]]] = None) -> Dict[str, torch.Tensor]:
     """[TRL collator semantics, SURVEY.md a3] truncate to ``max_len``, right-pad ``input_ids`` with
     the pad id, ``attention_mask`` with 0 and ``labels`` with -100.  Padding is the only mask the
     reference produces for plain ``messages`` data."""
@@ -193,16 +201,49 @@ def collate(samples: List[List[int]], pad_id: int, max_len: int, pad_to: Optiona
         input_ids[i, : len(s)] = t
         attn[i, : len(s)] = 1
         labels[i, : len(s)] = t
+        if masks is not None:  # completion-only loss: score the assistant's tokens only
+            keep = torch.tensor(masks[i][: len(s)], dtype=torch.bool)
+            labels[i, : len(s)] = torch.where(keep, t, torch.full_like(t, -100))
     return {"input_ids": input_ids, "attention_mask": attn, "labels": labels}
+
+
+def collate_flattened(samples: List[List[int]], max_len: int, masks: Optional[List[List[int]]] = None,
+                      separator_id: int = -100) -> Dict[str, Any]:
+    """Padding-free batch, as ``transformers.DataCollatorWithFlattening(return_flash_attn_kwargs=True)``
+    builds it (SP/transformers/data/data_collator.py:1364-1470): the samples are concatenated into one
+    ``[1, total]`` row, ``position_ids`` restart at every sample, the first label of every sample is
+    ``separator_id`` (:1426-1428) so no sample is scored against its predecessor, and the FlashAttention
+    varlen arguments (``cu_seq_lens_*`` int32, ``max_length_*`` int) ride along.  ``masks`` (0/1 per
+    token) additionally turn non-assistant tokens into -100 (completion-only loss)."""
+    samples = [s[:max_len] for s in samples]
+    ids: List[int] = []
+    labels: List[int] = []
+    pos: List[int] = []
+    cu = [0]
+    for i, smp in enumerate(samples):
+        lab = list(smp)
+        if masks is not None:
+            lab = [t if m else -100 for t, m in zip(smp, masks[i][:max_len])]
+        ids += smp
+        labels += [separator_id] + lab[1:]
+        pos += list(range(len(smp)))
+        cu.append(cu[-1] + len(smp))
+    longest = max(len(smp) for smp in samples)
+    return {"input_ids": torch.tensor([ids], dtype=torch.int64), "labels": torch.tensor([labels], dtype=torch.int64),
+            "position_ids": torch.tensor([pos], dtype=torch.int64),
+            "cu_seq_lens_q": torch.tensor(cu, dtype=torch.int32), "cu_seq_lens_k": torch.tensor(cu, dtype=torch.int32),
+            "max_length_q": longest, "max_length_k": longest}
 
 
 class ShardedBatches:
     """Per-rank micro-batch iterator: shuffles with the epoch seed, shards by rank, drops the
     ragged tail (``dataloader_drop_last=True``, training.py:281)."""
 
-    def __init__(self, tokens: List[List[int]], batch_size: int, rank: int, world: int, pad_id: int, max_len: int, seed: int):
+    def __init__(self, tokens: List[List[int]], batch_size: int, rank: int, world: int, pad_id: int, max_len: int, seed: int,
+                 masks: Optional[List[List[int]]] = None, padding_free: bool = False):
         self.tokens, self.bs, self.rank, self.world = tokens, batch_size, rank, world
         self.pad_id, self.max_len, self.seed = pad_id, max_len, seed
+        self.masks, self.padding_free = masks, padding_free
 
     def __len__(self) -> int:
         return len(self.tokens) // (self.bs * self.world)
@@ -213,7 +254,12 @@ class ShardedBatches:
         per_step = self.bs * self.world
         for b in range(len(self)):
             chunk = perm[b * per_step: (b + 1) * per_step][self.rank * self.bs: (self.rank + 1) * self.bs]
-            yield collate([self.tokens[i] for i in chunk], self.pad_id, self.max_len)
+            toks = [self.tokens[i] for i in chunk]
+            msk = [self.masks[i] for i in chunk] if self.masks is not None else None
+            if self.padding_free:
+                yield collate_flattened(toks, self.max_len, msk)
+            else:
+                yield collate(toks, self.pad_id, self.max_len, masks=msk)
 
 
 # --------------------------------------------------------------------------------------------
@@ -319,7 +365,7 @@ class MiniSFTTrainer(FusedCELossMixin):
         """trainer.py:1867-1936 for this configuration: H2D, compute_loss, backward.  No division
         by the accumulation steps: the loss is already normalised by the window's token count."""
         self.model_wrapped.train()
-        inputs = {k: v.to(self.device, non_blocking=True) for k, v in inputs.items()}
+        inputs = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in inputs.items()}
         if self.loss_impl is not None:
             loss = self.loss_impl(self.model_wrapped, inputs, num_items_in_batch)
             if num_items_in_batch is not None and self.args.average_tokens_across_devices:
@@ -352,7 +398,7 @@ class MiniSFTTrainer(FusedCELossMixin):
                     ctx = contextlib.nullcontext() if (sync or self.world == 1) else self.model_wrapped.no_sync()
                     with ctx:  # trainer.py:1725-1733 -> DDP.no_sync
                         tr_loss += self.training_step(inputs, num_items)
-                    tokens_seen += int(inputs["attention_mask"].sum())
+                    tokens_seen += int(inputs["attention_mask"].sum()) if "attention_mask" in inputs else inputs["input_ids"].numel()
                 if self.fused_tail:
                     grad_norm = self.optimizer.clip_and_step(args.max_grad_norm)
                 else:
@@ -405,9 +451,18 @@ def build_trainer(model: nn.Module, settings: SFTSettings, train_rows, val_rows,
                                eval_dataset=[format_prompt(r) for r in val_rows], callbacks=list(callbacks))
     except ImportError:
         pass
-    tok = lambda rows: [tokenizer.apply_chat_template(format_prompt(r)["messages"]) for r in rows]
-    mk = lambda rows, bs: ShardedBatches(tok(rows), bs, rank, world, tokenizer.pad_token_id,
-                                         settings.max_seq_length, settings.seed)
+    completion_only = os.getenv("COMPLETION_ONLY", "0") == "1" and isinstance(tokenizer, ByteChatTokenizer)
+
+    def mk(rows, bs):
+        msgs = [format_prompt(r)["messages"] for r in rows]
+        if completion_only:
+            pairs = [tokenizer.apply_chat_template(m, return_assistant_mask=True) for m in msgs]
+            toks, masks = [p[0] for p in pairs], [p[1] for p in pairs]
+        else:
+            toks, masks = [tokenizer.apply_chat_template(m) for m in msgs], None
+        return ShardedBatches(toks, bs, rank, world, tokenizer.pad_token_id, settings.max_seq_length, settings.seed,
+                              masks=masks, padding_free=settings.packing)
+
     return MiniSFTTrainer(model, settings, mk(train_rows, settings.per_device_train_batch_size),
                           mk(val_rows, settings.per_device_eval_batch_size), callbacks=callbacks, **mini_kwargs)
 

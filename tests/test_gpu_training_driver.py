@@ -52,6 +52,17 @@ def test_driver_single_gpu(cuda_device, tmp_path):
     _check(tmp_path, 1)
 
 
+def test_driver_padding_free_completion_only(cuda_device, tmp_path):
+    """PACKING=1: padding-free [1, total] batches with restarting position_ids and FlashAttention varlen
+    arguments; COMPLETION_ONLY=1: only the assistant's tokens carry labels, so most rows are compacted away."""
+    _write_parquet(tmp_path / "qa.parquet")
+    res = subprocess.run([sys.executable, "-m", "llm_fine_tune_distributed_b200.training"], cwd=ROOT,
+                         env=_env(tmp_path, WORLD_SIZE="1", RANK="0", LOCAL_RANK="0", PACKING="1", COMPLETION_ONLY="1",
+                                  ATTN_IMPL="flash_attention_2"), capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    _check(tmp_path, 1)
+
+
 def test_driver_two_gpus_ddp(cuda_device, tmp_path):
     import torch
 

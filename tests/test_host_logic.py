@@ -104,3 +104,36 @@ def test_collate_and_settings(monkeypatch):
     assert s.per_device_train_batch_size == 28 and s.learning_rate == 2e-4  # lr x world, training.py:263
     assert s.ddp_backend == "nccl" and s.ddp_bucket_cap_mb == 50 and not s.ddp_find_unused_parameters
     assert s.gradient_accumulation_steps == 4 and s.max_seq_length == 1024 and s.max_grad_norm == 1.0
+
+
+def test_flattened_collator_matches_transformers():
+    """collate_flattened vs the real DataCollatorWithFlattening, key for key."""
+    from transformers import DataCollatorWithFlattening
+
+    from llm_fine_tune_distributed_b200.training import collate_flattened
+
+    samples = [[5, 6, 7, 8], [9, 10], [11, 12, 13, 14, 15, 16, 17]]
+    ref = DataCollatorWithFlattening(return_flash_attn_kwargs=True)([{"input_ids": s} for s in samples], return_tensors="pt")
+    got = collate_flattened(samples, max_len=100)
+    assert set(got) == set(ref)
+    for k in ref:
+        if torch.is_tensor(ref[k]):
+            assert got[k].dtype == ref[k].dtype and torch.equal(got[k], ref[k]), k
+        else:
+            assert got[k] == ref[k], k
+    assert got["labels"].tolist() == [[-100, 6, 7, 8, -100, 10, -100, 12, 13, 14, 15, 16, 17]]
+
+
+def test_completion_only_masks():
+    from llm_fine_tune_distributed_b200.training import ByteChatTokenizer, collate, collate_flattened, format_prompt
+
+    tok = ByteChatTokenizer(128256)
+    msgs = format_prompt({"full-question": "q?", "answer": "an answer"})["messages"]
+    ids, mask = tok.apply_chat_template(msgs, return_assistant_mask=True)
+    assert ids == tok.apply_chat_template(msgs) and len(ids) == len(mask)
+    n_assistant = len("an answer<|im_end|>\n".encode()) + 1           # assistant body + eos
+    assert sum(mask) == n_assistant and mask[-1] == 1 and mask[0] == 0
+    batch = collate([ids], pad_id=0, max_len=4096, masks=[mask])
+    assert int((batch["labels"] != -100).sum()) == n_assistant
+    flat = collate_flattened([ids, ids], 4096, masks=[mask, mask])
+    assert int((flat["labels"] != -100).sum()) == 2 * n_assistant and flat["position_ids"][0, len(ids)] == 0

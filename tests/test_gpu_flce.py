@@ -250,3 +250,40 @@ def test_flce_is_bitwise_deterministic(cuda_device):
     torch.cuda.synchronize()
     for (s0, l0, dx0, dw0), (s1, l1, dx1, dw1) in ((runs[0], runs[2]), (runs[1], runs[3])):
         assert s0 == s1 and torch.equal(l0, l1) and torch.equal(dx0, dx1) and torch.equal(dw0, dw1)
+
+
+def test_flce_random_shape_sweep(cuda_device):
+    """Seeded sweep over ragged shapes (rows, hidden and vocabulary not multiples of any tile size),
+    mask densities, slab widths, compaction on/off and both engine variants, against the oracle."""
+    import random
+
+    from llm_fine_tune_distributed_b200 import _cabi, ops
+
+    rng = random.Random(1234)
+    try:
+        for i in range(24):
+            N = rng.choice([1, 7, 127, 129, 255, 257, 500, 777])
+            H = 8 * rng.randint(1, 40)
+            V = 8 * rng.randint(2, 300)
+            masked = rng.choice([0.0, 0.3, 0.9])
+            skip = rng.random() < 0.5
+            chunk = rng.choice([0, 256, 512])
+            _cabi.set_cta_group(rng.choice([1, 2]))
+            x, w, labels = _case(N, H, V, masked, seed=1000 + i, device=cuda_device)
+            n_valid = int((labels != -100).sum())
+            denom = torch.tensor(max(n_valid, 1), dtype=torch.int64, device=cuda_device)
+            xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+            loss = ops.fused_linear_cross_entropy(xg, wg, labels.to(torch.int32), denom, skip_ignored_rows=skip,
+                                                  chunk_cols=chunk)
+            loss.backward()
+            ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, float(denom))
+            torch.cuda.synchronize()
+            tag = f"case {i}: N={N} H={H} V={V} masked={masked} skip={skip} chunk={chunk}"
+            assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item()) + 1e-7, tag
+            if n_valid > 0:
+                assert _cos(xg.grad, ref_dx) >= 0.999 and _cos(wg.grad, ref_dw) >= 0.999, tag
+            else:
+                assert torch.count_nonzero(xg.grad) == 0 and torch.count_nonzero(wg.grad) == 0, tag
+            assert torch.isfinite(xg.grad.float()).all() and torch.isfinite(wg.grad.float()).all(), tag
+    finally:
+        _cabi.set_cta_group(2)

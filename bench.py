@@ -382,7 +382,8 @@ def run_b200(args) -> dict:
                 "last_loss": last_loss},
         "gpu_launches": launches,
         "roofline": {
-            "kernel": "gemm_tcgen05_kernel<FwdSoftmaxEpi> (+ row merge and loss reduce), N=8192 x H=2048 x V=128256",
+            "kernel": "gemm_tcgen05_2cta_kernel<FwdSoftmaxEpi> (+ label compaction, row merge and loss reduce: the whole "
+                      f"b200sft_flce_fwd call), N={N} x H={H} x V={V}",
             "bound": "tensor", "achieved": round(achieved, 1), "peak": peaks["sustained"], "unit": "TFLOP/s",
             "frac": round(achieved / peaks["sustained"], 4), "traffic": traffic,
             "peak_kind": "bf16 sustained, " + peaks["kind"], "algorithmic_flops_per_launch": fwd_flops,

@@ -219,10 +219,26 @@ def run_b200(args) -> dict:
     if world > 1:
         wrapped = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], bucket_cap_mb=50,
                                                             find_unused_parameters=False)
-        if args.comm == "nvlink":
-            hook_state = B200NvlinkState.for_model(model, None)
+        comm = os.environ.get("B200SFT_COMM", args.comm)
+        hook_state = None
+        if comm in ("auto", "nvlink"):
+            # symmetric-memory arena + rendezvous is a collective; every rank must end up on the same hook
+            try:
+                hook_state = B200NvlinkState.for_model(model, None)
+                ok = torch.ones((), device=dev)
+            except Exception as e:  # no symmetric memory on this box / torch build
+                if comm == "nvlink":
+                    raise
+                print(f"[rank {rank}] NVLink hook unavailable ({type(e).__name__}: {e}); using the NCCL hook", file=sys.stderr)
+                ok = torch.zeros((), device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok) < 1:
+                hook_state = None
+        if hook_state is not None:
+            args.comm = "nvlink"
             wrapped.register_comm_hook(hook_state, b200_nvlink_allreduce_hook)
         else:
+            args.comm = "nccl"
             hook_state = B200HookState(None)
             wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
         wrapped._b200sft_hook = True
@@ -485,9 +501,10 @@ def main():
     ap.add_argument("--attn", default="auto")
     ap.add_argument("--tail", default="b200", choices=["b200", "torch"],
                     help="step tail: this library's fused grad-norm clip + AdamW kernels, or torch's clip_grad_norm_ + fused AdamW")
-    ap.add_argument("--comm", default="nccl", choices=["nccl", "nvlink"],
-                    help="N>1: gradient hook = scale kernel + NCCL allreduce (default), or this library's fused "
-                         "NVLink reduce+scale kernel over symmetric memory")
+    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink"],
+                    help="N>1: gradient hook.  nvlink = this library's fused NVLink reduce+scale kernel over symmetric "
+                         "memory; nccl = scale kernel + NCCL allreduce; auto (default) = nvlink when symmetric memory "
+                         "can be set up on every rank, else nccl.  Env B200SFT_COMM overrides.")
     ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
                     help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
     ap.add_argument("--cpu-tokens", type=int, default=256)

@@ -507,7 +507,8 @@ def main():
                          "can be set up on every rank, else nccl.  Env B200SFT_COMM overrides.")
     ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
                     help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
-    ap.add_argument("--cpu-tokens", type=int, default=256)
+    ap.add_argument("--cpu-tokens", type=int, default=1024,
+                    help="CPU baseline / reference arm: tokens in the bounded sample (one row of the workload by default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")
     ap.add_argument("--no-clocks", action="store_true", help="profiling runs only: do not spawn the nvidia-smi sampler")

@@ -137,3 +137,20 @@ def test_completion_only_masks():
     assert int((batch["labels"] != -100).sum()) == n_assistant
     flat = collate_flattened([ids, ids], 4096, masks=[mask, mask])
     assert int((flat["labels"] != -100).sum()) == 2 * n_assistant and flat["position_ids"][0, len(ids)] == 0
+
+
+def test_patched_model_saves_and_reloads_as_stock(tiny, tmp_path):
+    """The head swap must not leak into checkpoints: save_pretrained on the patched model, then a
+    stock from_pretrained, gives the same logits (training.py:309-312 saves the best model this way)."""
+    from transformers import SmolLM3ForCausalLM
+
+    from llm_fine_tune_distributed_b200 import install_fused_head
+
+    install_fused_head(tiny)
+    ids = torch.randint(0, 512, (1, 6), generator=torch.Generator().manual_seed(2))
+    before = tiny(input_ids=ids).logits
+    tiny.save_pretrained(tmp_path / "ckpt")
+    again = SmolLM3ForCausalLM.from_pretrained(tmp_path / "ckpt", dtype=torch.bfloat16, attn_implementation="eager").eval()
+    assert type(again.lm_head) is torch.nn.Linear
+    assert again.lm_head.weight.data_ptr() == again.model.embed_tokens.weight.data_ptr()
+    assert torch.equal(again(input_ids=ids).logits, before)

@@ -153,4 +153,8 @@ def test_patched_model_saves_and_reloads_as_stock(tiny, tmp_path):
     again = SmolLM3ForCausalLM.from_pretrained(tmp_path / "ckpt", dtype=torch.bfloat16, attn_implementation="eager").eval()
     assert type(again.lm_head) is torch.nn.Linear
     assert again.lm_head.weight.data_ptr() == again.model.embed_tokens.weight.data_ptr()
-    assert torch.equal(again(input_ids=ids).logits, before)
+    sd0, sd1 = tiny.state_dict(), again.state_dict()
+    assert list(sd0) == list(sd1) and all(torch.equal(sd0[k], sd1[k]) for k in sd0)
+    # (logits agree to bf16 resolution only: the fixture's .to(bfloat16) also cast the rotary inv_freq buffer,
+    # which a fresh from_pretrained keeps in fp32 -- stock transformers behaviour, independent of the head swap)
+    assert torch.allclose(again(input_ids=ids).logits.float(), before.float(), atol=2e-2)

@@ -243,7 +243,8 @@ enum StoreMode { STORE_BF16 = 0, STORE_F32 = 1, ACCUM_F32 = 2, ACCUM_F32_OUT_BF1
 struct StoreEpi {
   struct Params {
     CUtensorMap out_map;  // [rows][cols] bf16 output view, box 64 x 32 (modes 0, 3)
-    float* acc;           // [M][ld] fp32 (modes 1, 2, 3)
+    float* acc;           // [M][ld] fp32 (modes 1, 2, 3); K-split ks uses acc + ks * split_stride
+    size_t split_stride;  // elements between the per-split accumulators (0 when the GEMM is not split)
     int ld;
     int mode;
   };
@@ -265,7 +266,7 @@ struct StoreEpi {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = (row < M) ? __uint_as_float(acc[j]) : 0.f;
     if (p.mode != STORE_BF16 && row < M) {  // fp32 accumulator across launches (only used with long K: cheap)
-      float* a = p.acc + static_cast<size_t>(row) * p.ld + col0;
+      float* a = p.acc + static_cast<size_t>(tc.ks) * p.split_stride + static_cast<size_t>(row) * p.ld + col0;
       if (col0 + 32 <= N) {
         float4* a4 = reinterpret_cast<float4*>(a);
         if (p.mode != STORE_F32) {
@@ -463,6 +464,29 @@ __global__ void scatter_rows_kernel(const __nv_bfloat16* __restrict__ dxc, const
   }
 }
 
+// dX = bf16( sum over the K-split accumulators ).  The number of live splits is recomputed from the
+// same inputs the GEMM kernel used (live rows -> tiles -> choose_k_splits), so nothing is read back.
+__global__ void dx_combine_splits_kernel(const float* __restrict__ acc, size_t split_stride, int rows_cap, int H,
+                                         const int* __restrict__ n_rows_dev, int tile_rows, int tiles_n, int workers,
+                                         int max_splits, __nv_bfloat16* __restrict__ out) {
+  const int rows = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
+  const int tiles = ((rows + tile_rows - 1) / tile_rows) * tiles_n;
+  const int splits = choose_k_splits(tiles, workers, max_splits);
+  const size_t nvec = static_cast<size_t>(rows) * H / 4;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < nvec;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(acc)[i];
+    for (int s = 1; s < splits; ++s) {
+      const float4 t = reinterpret_cast<const float4*>(acc + s * split_stride)[i];
+      v.x += t.x;
+      v.y += t.y;
+      v.z += t.z;
+      v.w += t.w;
+    }
+    reinterpret_cast<uint2*>(out)[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+  }
+}
+
 // =============================================================================================
 // Host side
 // =============================================================================================
@@ -535,9 +559,19 @@ constexpr int GROUP_M_ROWS = 8192;
 int g_cta_group = 2;
 
 // BN = output tile width of the pair engine (256; 128 is implemented and tested but slower, see DX_TILE_N).
+// Number of persistent workers (CTAs, or CTA pairs) a GEMM of this output shape is launched with.
+int gemm_workers(int M, int N, int bn = BLOCK_N) {
+  const bool paired = (g_cta_group == 2);
+  const int tile_m = paired ? pair::TILE_M : BLOCK_M;
+  const long long tiles = static_cast<long long>((M + tile_m - 1) / tile_m) * ((N + bn - 1) / bn);
+  const int max_w = paired ? num_sms() / 2 : num_sms();
+  return static_cast<int>(tiles < max_w ? tiles : max_w);
+}
+
 template <class Epi, bool A_MN, bool B_MN, int BN = 256>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
-                const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0) {
+                const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0,
+                int max_k_splits = 1) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
   const bool paired = (g_cta_group == 2);
   const int bn = paired ? BN : BLOCK_N;  // the single-CTA engine has one tile shape
@@ -558,6 +592,7 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.group_m = s.tiles_m < group ? s.tiles_m : group;
   s.dyn_rows = dyn_rows;
   s.dyn_is_k = dyn_is_k;
+  s.max_k_splits = max_k_splits;
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
   if (!paired) {
     auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
@@ -713,6 +748,16 @@ int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, in
   return B200SFT_OK;
 }
 
+// K-splits reserved for the dX GEMM: it has (N/tile rows) x (H/256) tiles, each with a very long K, so
+// when that count is small relative to the workers, wave quantisation costs up to 14 %.  Up to 4
+// splits (each with its own fp32 accumulator) when the GEMM has fewer than 16 tiles per worker.
+int dx_max_k_splits(int N, int H) {
+  const int workers = gemm_workers(N, H, DX_TILE_N);
+  const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
+  const long long tiles = static_cast<long long>((N + tile_m - 1) / tile_m) * ((H + DX_TILE_N - 1) / DX_TILE_N);
+  return tiles >= 16LL * workers ? 1 : 4;
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -780,7 +825,9 @@ size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols) {
   if (N <= 0 || H <= 0 || V <= 0) return 0;
   const int c = resolve_slab_cols(N, V, chunk_cols);
   size_t b = align_up(static_cast<size_t>(N) * c * sizeof(__nv_bfloat16), 1024);  // dlogits slab
-  if (c < V) b += align_up(static_cast<size_t>(N) * H * sizeof(float), 1024);     // fp32 dX accumulator
+  const int splits = dx_max_k_splits(N, H);
+  if (c < V || splits > 1)  // fp32 dX accumulator(s): across slabs and / or across K-splits
+    b += static_cast<size_t>(splits) * align_up(static_cast<size_t>(N) * H * sizeof(float), 1024);
   return b;
 }
 
@@ -804,10 +851,12 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
 
   const int slab = resolve_slab_cols(N, V, chunk_cols);
   const int num_slabs = (V + slab - 1) / slab;
+  const int dx_splits = dx_max_k_splits(N, H);
+  const size_t dx_split_stride = align_up(static_cast<size_t>(N) * H * sizeof(float), 1024) / sizeof(float);
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   __nv_bfloat16* dlog = reinterpret_cast<__nv_bfloat16*>(ws);
   ws += align_up(static_cast<size_t>(N) * slab * sizeof(__nv_bfloat16), 1024);
-  float* dx_acc = (num_slabs > 1) ? reinterpret_cast<float*>(ws) : nullptr;
+  float* dx_acc = (num_slabs > 1 || dx_splits > 1) ? reinterpret_cast<float*>(ws) : nullptr;
 
   const __nv_bfloat16* wb = static_cast<const __nv_bfloat16*>(w);
   __nv_bfloat16* dwb = static_cast<__nv_bfloat16*>(dw);
@@ -837,8 +886,11 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = make_store_tmap(&sx.out_map, dx, N, H, H);
     if (rc != 0) return rc;
     sx.acc = dx_acc;
+    sx.split_stride = dx_splits > 1 ? dx_split_stride : 0;
     sx.ld = H;
-    if (num_slabs == 1)
+    if (dx_splits > 1)  // every K-split keeps its own fp32 chain across the slabs; summed after the loop
+      sx.mode = (si == 0) ? STORE_F32 : ACCUM_F32;
+    else if (num_slabs == 1)
       sx.mode = STORE_BF16;
     else if (si == 0)
       sx.mode = STORE_F32;
@@ -847,7 +899,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     else
       sx.mode = ACCUM_F32;
     rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream,
-                                                       n_rows_dev, 0);
+                                                       n_rows_dev, 0, dx_splits);
     if (rc != 0) return rc;
 
     // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every
@@ -856,10 +908,21 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = make_store_tmap(&sw.out_map, dwb + static_cast<size_t>(v0) * H, cols, H, H);
     if (rc != 0) return rc;
     sw.acc = nullptr;
+    sw.split_stride = 0;
     sw.ld = H;
     sw.mode = STORE_BF16;
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, n_rows_dev, 1);
     if (rc != 0) return rc;
+  }
+  if (dx_splits > 1) {
+    const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
+    const size_t nvec = static_cast<size_t>(N) * H / 4;
+    size_t blocks = (nvec + 255) / 256;
+    if (blocks > static_cast<size_t>(num_sms()) * 8) blocks = static_cast<size_t>(num_sms()) * 8;
+    dx_combine_splits_kernel<<<static_cast<unsigned int>(blocks), 256, 0, stream>>>(
+        dx_acc, dx_split_stride, N, H, n_rows_dev, tile_m, (H + DX_TILE_N - 1) / DX_TILE_N,
+        gemm_workers(N, H, DX_TILE_N), dx_splits, static_cast<__nv_bfloat16*>(dx));
+    B200_CUDA_CHECK(cudaGetLastError());
   }
   return B200SFT_OK;
 }
@@ -879,6 +942,7 @@ int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K
   int rc = make_store_tmap(&sp.out_map, c, M, N, ldc);
   if (rc != 0) return rc;
   sp.acc = nullptr;
+  sp.split_stride = 0;
   sp.ld = ldc;
   sp.mode = STORE_BF16;
   if (!a_mn_major && !b_mn_major) return launch_gemm<StoreEpi, false, false>(a, lda, b, ldb, M, N, K, 0, sp, stream);

@@ -46,11 +46,45 @@ struct GemmShape {
   // tensor maps were built for.
   const int* dyn_rows;
   int dyn_is_k;
+  // Split-K: when a GEMM has too few tiles to fill the workers evenly (dX: 256 tiles of K = 64k on 74 CTA
+  // pairs = 3.46 waves), each tile's K range is cut into `choose_k_splits(...)` <= max_k_splits pieces that
+  // become separate work units.  Every piece accumulates into its own fp32 buffer (TileCoord::ks selects
+  // it in the epilogue), so the result stays deterministic; the caller sums the buffers afterwards.
+  int max_k_splits;
 };
 
 struct TileCoord {
   int m0, n0, tile_m, tile_n;
+  int ks;  // K-split index of this work unit (0 when the GEMM is not split)
 };
+
+// Smallest power of two <= max_splits for which `tiles * splits` work units fill `workers` to >= 95 %
+// in whole rounds.  A pure function of its arguments: kernels, the host and the combine kernel agree.
+__host__ __device__ inline int choose_k_splits(int tiles, int workers, int max_splits) {
+  int s = 1;
+  while (s < max_splits) {
+    const long long units = static_cast<long long>(tiles) * s;
+    const long long rounds = (units + workers - 1) / workers;
+    if (units * 100 >= rounds * workers * 95) break;
+    s *= 2;
+  }
+  return s;
+}
+
+// Work unit -> (tile, k-split) and the unit's k-block range [kb0, kb1).
+struct UnitRange {
+  int tile, ks, kb0, kb1;
+};
+__device__ __forceinline__ UnitRange unit_range(int unit, int splits, int num_kb) {
+  UnitRange u;
+  u.tile = unit / splits;
+  u.ks = unit - u.tile * splits;
+  const int per = (num_kb + splits - 1) / splits;
+  u.kb0 = u.ks * per;
+  u.kb1 = u.kb0 + per < num_kb ? u.kb0 + per : num_kb;
+  if (u.kb1 < u.kb0) u.kb1 = u.kb0;
+  return u;
+}
 
 __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
   TileCoord c;
@@ -68,6 +102,7 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
   }
   c.m0 = c.tile_m * BLOCK_M;
   c.n0 = c.tile_n * BLOCK_N;
+  c.ks = 0;
   return c;
 }
 
@@ -113,6 +148,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
+  const int splits = choose_k_splits(num_tiles, gridDim.x, shape.max_k_splits > 0 ? shape.max_k_splits : 1);
+  const int num_units = num_tiles * splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -138,9 +175,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(shape, tile);
-        for (int kb = 0; kb < num_kb; ++kb) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const TileCoord tc = tile_coord(shape, ur.tile);
+        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -180,13 +218,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
+        const UnitRange ur = unit_range(unit, splits, num_kb);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
           const uint32_t a_addr = smem_u32(smem_a + stage * A_STAGE_BYTES);
@@ -195,7 +234,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
           for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
             const uint64_t da = make_smem_desc_sw128(a_addr + kk * A_KSTEP, A_LBO, 1024);
             const uint64_t db = make_smem_desc_sw128(b_addr + kk * B_KSTEP, B_LBO, 1024);
-            umma_bf16<1>(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+            umma_bf16<1>(d_tmem, da, db, idesc, (kb != ur.kb0 || kk != 0) ? 1u : 0u);
           }
           umma_commit<1>(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
           if (++stage == NUM_STAGES) {
@@ -213,8 +252,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     const int row_in_tile = quarter * 32 + lane;
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const TileCoord tc = tile_coord(shape, tile);
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
+      const UnitRange ur = unit_range(unit, splits, num_kb);
+      TileCoord tc = tile_coord(shape, ur.tile);
+      tc.ks = ur.ks;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       epi.tile_begin(tc, row_in_tile);
@@ -225,7 +266,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       for (int c = 0; c < BLOCK_N; c += 32) {
         uint32_t acc[32];
         __syncwarp();  // epilogue functors may diverge per row; tcgen05.ld is warp-collective
-        if (num_kb > 0) {
+        if (ur.kb1 > ur.kb0) {
           tmem_ld_32x32b_x32(taddr + c, acc);
           tmem_ld_wait();
         } else {  // empty contraction (no live rows): the accumulator was never written
@@ -297,6 +338,7 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile, in
   }
   c.m0 = c.tile_m * TILE_M + cta_rank * BLOCK_M;
   c.n0 = c.tile_n * BN;
+  c.ks = 0;
   return c;
 }
 
@@ -340,6 +382,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int num_pairs = gridDim.x >> 1;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
+  const int splits = choose_k_splits(num_tiles, num_pairs, shape.max_k_splits > 0 ? shape.max_k_splits : 1);
+  const int num_units = num_tiles * splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -365,10 +409,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
-        const TileCoord tc = tile_coord<BN>(shape, tile, cta_rank);
+      for (int unit = pair_id; unit < num_units; unit += num_pairs) {
+        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
         const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * CTA_STAGE_BYTES);  // both CTAs' bytes
           uint8_t* sa = smem_a + stage * A_BYTES;
@@ -405,13 +450,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+      for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
+        const UnitRange ur = unit_range(unit, splits, num_kb);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
         tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
           const uint32_t a_addr = smem_u32(smem_a + stage * A_BYTES);
@@ -420,7 +466,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
           for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
             const uint64_t da = make_smem_desc_sw128(a_addr + kk * A_KSTEP, A_LBO, 1024);
             const uint64_t db = make_smem_desc_sw128(b_addr + kk * B_KSTEP, B_LBO, 1024);
-            umma_bf16<2>(d_tmem, da, db, idesc, (kb | kk) != 0 ? 1u : 0u);
+            umma_bf16<2>(d_tmem, da, db, idesc, (kb != ur.kb0 || kk != 0) ? 1u : 0u);
           }
           umma_commit<2>(&empty_bar[stage], 0x3);  // frees the stage in both CTAs
           if (++stage == STAGES) {
@@ -438,8 +484,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     const int row_in_tile = quarter * 32 + lane;  // row within this CTA's 128-row half
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
-    for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
-      const TileCoord tc = tile_coord<BN>(shape, tile, cta_rank);
+    for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
+      const UnitRange ur = unit_range(unit, splits, num_kb);
+      TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
+      tc.ks = ur.ks;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       epi.tile_begin(tc, row_in_tile);
@@ -450,7 +498,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       for (int c = 0; c < BN; c += 32) {
         uint32_t acc[32];
         __syncwarp();
-        if (num_kb > 0) {
+        if (ur.kb1 > ur.kb0) {
           tmem_ld_32x32b_x32(taddr + c, acc);
           tmem_ld_wait();
         } else {

@@ -41,12 +41,15 @@ def test_version_and_workspace_queries(lib):
     need = lib.b200sft_flce_fwd_workspace_bytes(8192, 2048, 128256)
     assert need == 501 * 8192 * 8 + 2 * 8192 * 4
     assert lib.b200sft_flce_fwd_workspace_bytes(0, 2048, 128256) == 0
-    # backward: one [N, slab] bf16 dlogits slab (+ fp32 dX accumulator when V spans several slabs)
+    # backward: one [N, slab] bf16 dlogits slab + fp32 dX accumulators: one per K-split of the dX GEMM (4 when
+    # that GEMM has fewer than 16 tiles per worker, else 1 -- and none at all for a single unsplit slab)
     one = lib.b200sft_flce_bwd_workspace_bytes(4096, 2048, 128256, 0)       # 1 GiB budget: single slab
     two = lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 0)       # two slabs of 64256 columns
-    assert one == 4096 * 128256 * 2
-    assert two == 8192 * 64256 * 2 + 8192 * 2048 * 4
-    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 128256) == 8192 * 128256 * 2
+    big = lib.b200sft_flce_bwd_workspace_bytes(65536, 2048, 128256, 0)      # 16 slabs of 8192, dX not split
+    assert one == 4096 * 128256 * 2 + 4 * 4096 * 2048 * 4
+    assert two == 8192 * 64256 * 2 + 4 * 8192 * 2048 * 4
+    assert big == 65536 * 8192 * 2 + 65536 * 2048 * 4
+    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 128256) == 8192 * 128256 * 2 + 4 * 8192 * 2048 * 4
 
 
 def test_argument_validation_without_launching(lib):

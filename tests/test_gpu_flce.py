@@ -161,7 +161,10 @@ def test_flce_skip_ignored_rows_matches_dense_path_and_oracle(cuda_device, N, H,
     torch.cuda.synchronize()
     (l0, dx0, dw0), (l1, dx1, dw1) = outs
     assert abs(l0.item() - l1.item()) <= 1e-5 * max(abs(l0.item()), 1e-6)
-    assert torch.equal(dx0, dx1)                        # each dX row depends on its own row only
+    # each dX row depends on its own row only; the dense and the compacted GEMM may cut K into a different
+    # number of split-K pieces (they have different tile counts), so the fp32 sums can differ in the last bit
+    assert torch.allclose(dx0.float(), dx1.float(), rtol=2.0 ** -7, atol=1e-7)
+    assert n_valid == 0 or _cos(dx0, dx1) > 0.99999
     assert torch.count_nonzero(dx1[labels == -100]) == 0
     assert torch.allclose(dw0.float(), dw1.float(), rtol=2.0 ** -7, atol=1e-6)   # same sum, other order over rows
     ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, float(denom))

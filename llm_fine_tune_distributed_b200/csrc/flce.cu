@@ -24,7 +24,6 @@
 namespace b200 {
 
 constexpr float LOG2E = 1.4426950408889634f;
-constexpr float LN2 = 0.6931471805599453f;
 
 // =============================================================================================
 // Epilogues

@@ -2,10 +2,14 @@
 //
 //   D[M,N] (fp32, TMEM) = A[M,K] (bf16) * B[N,K]^T (bf16)
 //
-// One CTA per SM loops over 128x256 output tiles.  Warp 0 streams A/B k-blocks into a 4-deep
-// shared-memory ring with TMA (128-byte swizzle), warp 1 issues tcgen05.mma from one thread into
-// one of two 256-column TMEM accumulator stages, warps 2..5 drain the other stage with tcgen05.ld
-// and run the fused epilogue, so the epilogue of tile i overlaps the MMAs of tile i+1.  The
+// Two variants share the structure, the work-unit schedule and the epilogue functors:
+//   gemm_tcgen05_kernel       one CTA per SM on 128x256 tiles (cta_group::1), 4-deep ring;
+//   gemm_tcgen05_2cta_kernel  clusters of two CTAs on 256x256 tiles (cta_group::2), 6-deep ring -- the
+//                             default (see the second half of this file).
+// Warp 0 streams A/B k-blocks into the shared-memory ring with TMA (128-byte swizzle), warp 1 issues
+// tcgen05.mma from one thread into one of two 256-column TMEM accumulator stages, warps 2..5 drain
+// the other stage with tcgen05.ld and run the fused epilogue, so the epilogue of work unit i overlaps
+// the MMAs of unit i+1.  A work unit is an output tile, or one K-split of it (choose_k_splits).  The
 // epilogue is a functor; the LM-head/cross-entropy kernels differ only there (flce.cu).
 //
 // Either operand may be K-major (K contiguous in global memory) or MN-major (M or N contiguous):

@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--chunk-cols", type=int, default=0)
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--kernel-times", action="store_true", help="also print per-kernel device times (torch.profiler)")
     ap.add_argument("--skip-ignored", action="store_true", help="compact away ignore_index rows first (valid-row compaction)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -97,6 +98,17 @@ def main():
             t_f = time_ms(fwd, args.iters, args.warmup, flush)
             t_b = time_ms(bwd, args.iters, args.warmup, flush)
             fused_mem = torch.cuda.max_memory_allocated() - base_mem
+            if args.kernel_times:
+                from torch.profiler import ProfilerActivity, profile
+
+                with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                    for _ in range(3):
+                        fwd()
+                        bwd()
+                    torch.cuda.synchronize()
+                for e in sorted(prof.key_averages(), key=lambda e: -e.device_time_total):
+                    if e.device_time_total > 0:
+                        print(f"   {e.device_time_total / e.count / 1e3:8.3f} ms x{e.count:3d}  {e.key[:100]}")
             fl_f, fl_fb = 2.0 * N * H * V, 6.0 * N * H * V
             rec = {
                 "N": N, "H": H, "V": V, "masked": m, "chunk_cols": args.chunk_cols, "skip_ignored_rows": args.skip_ignored,

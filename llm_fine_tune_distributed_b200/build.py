@@ -19,7 +19,7 @@ HEADERS = ["sm100_ptx.cuh", "gemm_engine.cuh", "capi_common.h", "../../include/b
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-lineinfo", "-O3", "-std=c++17",
+    "-lineinfo", "-O3", "-std=c++17", "-t", "4",
     "-Xcompiler", "-fPIC", "-shared",
     "--cudart", "static",  # self-contained: shares the primary context (streams, pointers) with torch
 ]

@@ -308,31 +308,54 @@ struct StoreEpi {
 // Merge the per-vocabulary-tile (max, sumexp) partials of each row into lse, and emit the row's
 // loss term (lse - target logit) or 0 for ignored rows.  With `partials_ez` also the row's softmax
 // entropy and whether the target holds the row maximum (token accuracy).
-__global__ void flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ partials_ez,
-                                       const float* __restrict__ tgt_logit, const int32_t* __restrict__ labels,
-                                       int rows_cap, const int* __restrict__ n_rows_dev, int tiles_n, int ignore_index,
-                                       float* __restrict__ lse, float* __restrict__ row_loss,
-                                       float* __restrict__ row_entropy, unsigned char* __restrict__ row_correct) {
+constexpr int MERGE_ROWS = 32;   // rows per block
+constexpr int MERGE_LANES = 8;   // threads per row, each folding every 8th vocabulary tile
+
+__global__ void __launch_bounds__(MERGE_ROWS* MERGE_LANES)
+    flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ partials_ez,
+                           const float* __restrict__ tgt_logit, const int32_t* __restrict__ labels, int rows_cap,
+                           const int* __restrict__ n_rows_dev, int tiles_n, int ignore_index, float* __restrict__ lse,
+                           float* __restrict__ row_loss, float* __restrict__ row_entropy,
+                           unsigned char* __restrict__ row_correct) {
   const int M = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
-  const int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= M) return;
-  float m = -INFINITY;
-  for (int t = 0; t < tiles_n; ++t) m = fmaxf(m, partials[static_cast<size_t>(t) * rows_cap + row].x);
-  float s = 0.f, ez = 0.f;
-  for (int t = 0; t < tiles_n; ++t) {
-    const float2 pr = partials[static_cast<size_t>(t) * rows_cap + row];
-    const float f = exp2f((pr.x - m) * LOG2E);
-    s += pr.y * f;
-    if (partials_ez) ez += partials_ez[static_cast<size_t>(t) * rows_cap + row] * f;
+  const int r = threadIdx.x % MERGE_ROWS, g = threadIdx.x / MERGE_ROWS;
+  const int row = blockIdx.x * MERGE_ROWS + r;
+  // online merge of this lane's tiles: (m, s, ez) with s and ez relative to m
+  float m = -INFINITY, sum = 0.f, ez = 0.f;
+  if (row < M) {
+    for (int t = g; t < tiles_n; t += MERGE_LANES) {
+      const size_t at = static_cast<size_t>(t) * rows_cap + row;
+      const float2 pr = partials[at];
+      const float nm = fmaxf(m, pr.x);
+      const float fo = exp2f((m - nm) * LOG2E), fn = exp2f((pr.x - nm) * LOG2E);
+      sum = sum * fo + pr.y * fn;
+      if (partials_ez) ez = ez * fo + partials_ez[at] * fn;
+      m = nm;
+    }
   }
-  const float l = m + logf(s);
+  __shared__ float s_m[MERGE_LANES][MERGE_ROWS], s_s[MERGE_LANES][MERGE_ROWS], s_e[MERGE_LANES][MERGE_ROWS];
+  s_m[g][r] = m;
+  s_s[g][r] = sum;
+  s_e[g][r] = ez;
+  __syncthreads();
+  if (g != 0 || row >= M) return;
+  for (int k = 1; k < MERGE_LANES; ++k) {  // fixed order: deterministic
+    const float om = s_m[k][r];
+    if (om == -INFINITY) continue;  // that lane had no tiles
+    const float nm = fmaxf(m, om);
+    const float fo = exp2f((m - nm) * LOG2E), fn = exp2f((om - nm) * LOG2E);
+    sum = sum * fo + s_s[k][r] * fn;
+    ez = ez * fo + s_e[k][r] * fn;
+    m = nm;
+  }
+  const float l = m + logf(sum);
   lse[row] = l;
   const int lbl = labels[row];
   const bool valid = lbl != ignore_index;
   const float tgt = tgt_logit[row];
   row_loss[row] = valid ? (l - tgt) : 0.f;
   if (partials_ez) {
-    row_entropy[row] = valid ? (l - ez / s) : 0.f;
+    row_entropy[row] = valid ? (l - ez / sum) : 0.f;
     row_correct[row] = (valid && tgt >= m) ? 1 : 0;  // the target logit is the row maximum
   }
 }
@@ -538,6 +561,12 @@ int make_store_tmap(CUtensorMap* m, const void* base, int rows, int cols, int ld
   return make_tmap(m, base, static_cast<uint64_t>(cols), static_cast<uint64_t>(rows), static_cast<uint64_t>(ld), 64, 32);
 }
 
+int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev < 0 || dev >= 64) ? 0 : dev;
+}
+
 int num_sms() {
   static int sms[64] = {0};
   int dev = 0;
@@ -595,7 +624,12 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
   if (!paired) {
     auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
-    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    static bool smem_set[64] = {false};  // per template instantiation and device
+    const int dev = current_device();
+    if (!smem_set[dev]) {
+      B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+      smem_set[dev] = true;
+    }
     const int grid = static_cast<int>(tiles < num_sms() ? tiles : num_sms());
     kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(ta, tb, s, ep);
     B200_CUDA_CHECK(cudaGetLastError());
@@ -603,7 +637,12 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   }
   auto kern = gemm_tcgen05_2cta_kernel<Epi, A_MN, B_MN, BN>;
   constexpr int smem_bytes = pair::Cfg<BN>::SMEM_BYTES;
-  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  static bool smem_set[64] = {false};
+  const int dev = current_device();
+  if (!smem_set[dev]) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    smem_set[dev] = true;
+  }
   const int max_pairs = num_sms() / 2;
   const int pairs = static_cast<int>(tiles < max_pairs ? tiles : max_pairs);
   cudaLaunchConfig_t cfg = {};
@@ -736,7 +775,7 @@ int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, in
   }
   if (rc != 0) return rc;
 
-  flce_merge_rows_kernel<<<(N + 255) / 256, 256, 0, stream>>>(f.partials, f.partials_ez, f.tgt, labels, N, n_rows_dev,
+  flce_merge_rows_kernel<<<(N + MERGE_ROWS - 1) / MERGE_ROWS, MERGE_ROWS * MERGE_LANES, 0, stream>>>(f.partials, f.partials_ez, f.tgt, labels, N, n_rows_dev,
                                                                tiles_n, ignore_index, lse, f.row_loss, f.row_entropy,
                                                                f.row_correct);
   B200_CUDA_CHECK(cudaGetLastError());

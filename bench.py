@@ -366,10 +366,12 @@ def run_b200(args) -> dict:
     peaks = read_peaks()
     fwd_flops = 2.0 * N * H * V
     achieved = fwd_flops / (fwd_ms / 1e3) / 1e12
-    traffic = None
+    traffic = tensor_pct = None
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("flce_fwd_dram_bytes_per_launch")
+        prof = json.load(open(tp))
+        traffic = prof.get("flce_fwd_dram_bytes_per_launch")
+        tensor_pct = prof.get("flce_kernels_tensor_pipe_active_pct")
     probe = synthetic_window(0, GA, B, T, pin=False, workload=args.workload)
     h2d_bytes = sum(v.numel() * v.element_size() for mb in probe for v in mb.values() if torch.is_tensor(v))
     res = {
@@ -405,6 +407,7 @@ def run_b200(args) -> dict:
             "peak_kind": "bf16 sustained, " + peaks["kind"], "algorithmic_flops_per_launch": fwd_flops,
             "avg_launch_ms": round(fwd_ms, 4),
             "frac_of_burst_peak": round(achieved / peaks["burst"], 4),
+            "ncu_tensor_pipe_active_pct": tensor_pct,  # from the committed ncu --set full capture, not measured live
         },
         "flce_bwd": {"avg_call_ms": round(bwd_ms, 4), "algorithmic_flops_per_call": 4.0 * N * H * V,
                      "achieved_tflops": round(4.0 * N * H * V / (bwd_ms / 1e3) / 1e12, 1),

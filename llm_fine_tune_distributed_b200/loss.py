@@ -155,6 +155,7 @@ class FusedCELossMixin:
     b200sft_skip_ignored_rows: bool = True
     b200sft_token_stats: bool = False  # True: log mean_token_accuracy / entropy like TRL, without logits
     b200sft_register_comm_hook: bool = True
+    b200sft_nvlink_hook: bool = False  # True (or env B200SFT_COMM=nvlink): the fused NVLink reduce+scale kernel
 
     def _b200sft_prepare(self, model: nn.Module) -> None:
         inner = _unwrap(model)
@@ -163,9 +164,14 @@ class FusedCELossMixin:
                                self.b200sft_token_stats)
         if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)
                 and not getattr(model, "_b200sft_hook", False)):
+            import os
+
             from .comm_hook import register_b200_comm_hook
 
-            register_b200_comm_hook(model)
+            nvlink = self.b200sft_nvlink_hook or os.environ.get("B200SFT_COMM") == "nvlink"
+            # the first compute_loss call happens at the same point on every rank, which the symmetric-memory
+            # rendezvous of the NVLink hook needs
+            register_b200_comm_hook(model, nvlink_kernel=nvlink)
             model._b200sft_hook = True
 
     def _b200sft_num_processes(self) -> int:

@@ -63,13 +63,14 @@ def test_driver_padding_free_completion_only(cuda_device, tmp_path):
     _check(tmp_path, 1)
 
 
-def test_driver_two_gpus_ddp(cuda_device, tmp_path):
+@pytest.mark.parametrize("comm", ["nccl", "nvlink"])
+def test_driver_two_gpus_ddp(cuda_device, tmp_path, comm):
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     _write_parquet(tmp_path / "qa.parquet")
-    env = _env(tmp_path)
+    env = _env(tmp_path, B200SFT_COMM=comm)
     for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
         env.pop(k, None)
     res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",

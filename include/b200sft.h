@@ -152,8 +152,8 @@ int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels
  * an [N,V] tensor; dW slabs are final after one pass, dX accumulates in fp32 across slabs.
  *   lse       [N] fp32 from the forward call
  *   grad_out  fp32 scalar (device): upstream gradient of `loss`
- *   dx        [N,H] bf16 out
- *   dw        [V,H] bf16 out (overwritten)
+ *   dx        [N,H] bf16 out, or NULL to skip the dX GEMM
+ *   dw        [V,H] bf16 out (overwritten), or NULL to skip the dW GEMM (frozen head)
  *   chunk_cols  vocabulary columns of dlogits held in scratch at a time (rounded up to a multiple
  *               of 256; 0 = library default: about 1 GiB of scratch, split into equal slabs)
  *   n_rows_dev  as in b200sft_flce_fwd (compacted inputs; dx is then compact too)

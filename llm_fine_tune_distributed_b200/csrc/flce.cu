@@ -876,7 +876,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   int rc = check_dims(N, H, V);
   if (rc != 0) return rc;
-  if (!x || !w || !labels || !lse || !grad_out || !dx || !dw) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (!x || !w || !labels || !lse || !grad_out) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  if (!dx && !dw) return fail(B200SFT_ERR_INVALID, "at least one of dx / dw must be requested");
   if (denom_mode == B200SFT_DENOM_VALID)
     return fail(B200SFT_ERR_INVALID,
                 "backward takes the valid-row count as a device scalar: pass n_valid from the forward call with "
@@ -920,6 +921,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     if (rc != 0) return rc;
 
     // (2) dX[N,H] (+)= dlogits[N,cols] . W[v0:v0+cols, :]     A K-major, B = W rows read MN-major
+    if (dx != nullptr) {
     StoreEpi::Params sx;
     rc = make_store_tmap(&sx.out_map, dx, N, H, H);
     if (rc != 0) return rc;
@@ -939,9 +941,11 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream,
                                                        n_rows_dev, 0, dx_splits);
     if (rc != 0) return rc;
+    }
 
     // (3) dW[v0:v0+cols, :] = dlogits^T[cols,N] . X[N,H]      both operands read MN-major; K spans every
     //     row, so each dW slab is final after one GEMM (no accumulation across slabs)
+    if (dw == nullptr) continue;  // frozen head: only dX was asked for
     StoreEpi::Params sw;
     rc = make_store_tmap(&sw.out_map, dwb + static_cast<size_t>(v0) * H, cols, H, H);
     if (rc != 0) return rc;
@@ -952,7 +956,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, n_rows_dev, 1);
     if (rc != 0) return rc;
   }
-  if (dx_splits > 1) {
+  if (dx_splits > 1 && dx != nullptr) {
     const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
     const size_t nvec = static_cast<size_t>(N) * H / 4;
     size_t blocks = (nvec + 255) / 256;

@@ -180,9 +180,11 @@ def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: 
 def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                   grad_out: torch.Tensor, scale: float = 1.0, denom: Optional[torch.Tensor] = None,
                   ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0,
-                  n_rows: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+                  n_rows: Optional[torch.Tensor] = None, need_dx: bool = True, need_dw: bool = True
+                  ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """dx [N,H] bf16, dw [V,H] bf16 for the loss produced by :func:`flce_forward` (with compacted
-    inputs and ``n_rows``, dx is compact too: expand it with :func:`scatter_rows`)."""
+    inputs and ``n_rows``, dx is compact too: expand it with :func:`scatter_rows`).  ``need_dx`` /
+    ``need_dw`` False skip the corresponding GEMM and return None in its place."""
     N, H, V = _check_flce_inputs(x, w, labels)
     _require_cuda(lse, grad_out)
     if lse.dtype != torch.float32 or lse.shape != (N,):
@@ -193,14 +195,17 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
     with torch.cuda.device(x.device):
         ws_bytes = lib.b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_cols)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
-        dx = torch.empty_like(x)
-        dw = torch.empty_like(w)
+        if not (need_dx or need_dw):
+            return None, None
+        dx = torch.empty_like(x) if need_dx else None
+        dw = torch.empty_like(w) if need_dw else None
         ev = STATS.begin("flce_bwd", x.device)
         check(lib.b200sft_flce_bwd(_ptr(x), _ptr(w), _ptr(labels), _ptr(lse), _ptr(grad_out), N, H, V,
                                    ignore_index, float(scale), mode, _ptr(denom), flags, chunk_cols, _ptr(n_rows),
                                    _ptr(dx), _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
         STATS.end(ev, x.device)
-        STATS.kernel_launches += 3 * _bwd_num_slabs(N, V, chunk_cols)  # dlogits, dX, dW GEMMs per vocabulary slab
+        STATS.kernel_launches += (1 + int(need_dx) + int(need_dw)) * _bwd_num_slabs(N, V, chunk_cols) + int(need_dx)
+        # per vocabulary slab: dlogits GEMM + dX GEMM + dW GEMM; plus the split-K combine for dX (when split)
     return dx, dw
 
 
@@ -333,13 +338,17 @@ def _(x, w, labels, scale, denom, reduction_mean, ignore_index, flags, n_rows, w
 @torch.library.custom_op("b200sft::flce_bwd", mutates_args=())
 def _flce_bwd_op(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
                  grad_out: torch.Tensor, scale: float, denom: Optional[torch.Tensor], ignore_index: int,
-                 flags: int, chunk_cols: int, n_rows: Optional[torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
-    return flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows)
+                 flags: int, chunk_cols: int, n_rows: Optional[torch.Tensor], need_dx: bool, need_dw: bool
+                 ) -> Tuple[torch.Tensor, torch.Tensor]:
+    dx, dw = flce_backward(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows,
+                           need_dx, need_dw)
+    # custom ops return tensors: an empty tensor stands for "not computed"
+    return (dx if dx is not None else x.new_empty(0)), (dw if dw is not None else w.new_empty(0))
 
 
 @_flce_bwd_op.register_fake
-def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows):
-    return torch.empty_like(x), torch.empty_like(w)
+def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols, n_rows, need_dx, need_dw):
+    return (torch.empty_like(x) if need_dx else x.new_empty(0)), (torch.empty_like(w) if need_dw else w.new_empty(0))
 
 
 class _FusedLinearCrossEntropy(torch.autograd.Function):
@@ -362,11 +371,11 @@ class _FusedLinearCrossEntropy(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_loss, *_unused):
         xk, w, lk, lse, bwd_denom, pos, n_rows = ctx.saved_tensors
+        need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         dx, dw = torch.ops.b200sft.flce_bwd(xk, w, lk, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
-                                            ctx.flags, ctx.chunk_cols, n_rows)
-        if pos is not None:
-            dx = scatter_rows(dx, pos)
-        return dx, dw, None, None, None, None, None, None, None, None, None
+                                            ctx.flags, ctx.chunk_cols, n_rows, need_dx, need_dw)
+        dx = None if not need_dx else (scatter_rows(dx, pos) if pos is not None else dx)
+        return dx, (dw if need_dw else None), None, None, None, None, None, None, None, None, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,

@@ -290,3 +290,26 @@ def test_flce_random_shape_sweep(cuda_device):
             assert torch.isfinite(xg.grad.float()).all() and torch.isfinite(wg.grad.float()).all(), tag
     finally:
         _cabi.set_cta_group(2)
+
+
+def test_flce_backward_skips_unneeded_gradients(cuda_device):
+    """Frozen head (no dW) or frozen trunk (no dX): the corresponding GEMM is skipped and the other
+    gradient is unchanged."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = _case(512, 128, 2048, 0.3, seed=8, device=cuda_device)
+    lab = labels.to(torch.int32)
+    denom = torch.tensor(int((labels != -100).sum()), dtype=torch.int64, device=cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    ops.fused_linear_cross_entropy(xg, wg, lab, denom).backward()
+    for skip in (False, True):
+        x1 = x.clone().requires_grad_(True)
+        ops.STATS.reset()
+        ops.fused_linear_cross_entropy(x1, w, lab, denom, skip_ignored_rows=skip).backward()      # head frozen
+        launches_dx_only = ops.STATS.kernel_launches
+        assert torch.allclose(x1.grad.float(), xg.grad.float(), rtol=2.0 ** -7, atol=1e-7)
+        w1 = w.clone().requires_grad_(True)
+        ops.STATS.reset()
+        ops.fused_linear_cross_entropy(x, w1, lab, denom, skip_ignored_rows=skip).backward()      # only the head trains
+        assert torch.allclose(w1.grad.float(), wg.grad.float(), rtol=2.0 ** -7, atol=1e-7)
+        assert ops.STATS.kernel_launches < launches_dx_only + 2

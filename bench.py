@@ -257,6 +257,8 @@ def run_b200(args) -> dict:
 
     seam = Seam()
 
+    bwd_done = [] if (world > 1 and isinstance(hook_state, B200NvlinkState)) else None
+
     def opt_step(window_dev) -> torch.Tensor:
         """One optimizer step on device-resident micro-batches; returns the summed loss."""
         n_items = sum(mb["labels"].ne(-100).sum() for mb in window_dev)  # Trainer._get_num_items_in_batch
@@ -269,6 +271,10 @@ def run_b200(args) -> dict:
             with ctx:
                 loss = seam.compute_loss(wrapped, dict(mb), num_items_in_batch=n_items)
                 loss.backward()
+            if last and bwd_done is not None:   # backward() returns after DDP has waited for every bucket
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                bwd_done.append(ev)
             total_loss += loss.detach()
         if args.tail == "b200":
             opt.clip_and_step(1.0)          # grad-norm + clip + AdamW in this library's multi-tensor kernels
@@ -319,7 +325,23 @@ def run_b200(args) -> dict:
     if rank == 0 and not args.no_clocks:
         sampler.start()
     ops.STATS.reset(with_events=True)
+    if bwd_done is not None:
+        hook_state.timeline = []
+        bwd_done.clear()
     ms_step, wall_dev, _ = timed(args.steps, e2e=False, first_step=100)
+    comm_times = None
+    if bwd_done is not None and hook_state.timeline:
+        # per step: buckets in arrival order; the last one is handed over when backward compute ends, so the time
+        # from that hand-over to the end of backward() is communication the step could not hide
+        tl, per = hook_state.timeline, len(hook_state.timeline) // max(len(bwd_done), 1)
+        exposed = [tl[(i + 1) * per - 1][0].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
+        busy = [sum(a.elapsed_time(b) for a, b, _ in tl[i * per:(i + 1) * per]) for i in range(len(bwd_done))]
+        big = max(tl, key=lambda t: t[2])
+        comm_times = {"exposed_ms_per_step": round(sum(exposed) / len(exposed), 3),
+                      "hook_busy_ms_per_step": round(sum(busy) / len(busy), 3),
+                      "largest_bucket": {"MiB": round(big[2] / 2**20, 1), "ms": round(big[0].elapsed_time(big[1]), 3),
+                                         "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1)}}
+        hook_state.timeline = None
     launches = ops.STATS.kernel_launches
     fwd_ms, bwd_ms = ops.STATS.mean_ms("flce_fwd"), ops.STATS.mean_ms("flce_bwd")
     ops.STATS.reset(with_events=False)
@@ -419,6 +441,8 @@ def run_b200(args) -> dict:
         res["comm"] = {"hook": args.comm, "path": getattr(hook_state, "path_used", "nccl"),
                        "buckets_per_step": round(hook_state.buckets_seen / max(n_steps, 1), 2),
                        "bytes_reduced_per_step": round(hook_state.bytes_reduced / max(n_steps, 1))}
+        if comm_times:
+            res["comm"].update(comm_times)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         res["cpu_baseline"] = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=1)
     if world > 1:

@@ -44,6 +44,10 @@ class B200HookState:
         self._streams = {}
         self.buckets_seen = 0
         self.bytes_reduced = 0
+        # measurement aid: when `timeline` is a list, every hook call appends
+        # (event recorded on the autograd stream when the bucket was handed over, event recorded on the side
+        # stream when its reduction finished, bucket bytes)
+        self.timeline = None
 
     def group(self) -> dist.ProcessGroup:
         return self.process_group if self.process_group is not None else dist.group.WORLD
@@ -54,6 +58,22 @@ class B200HookState:
             s = torch.cuda.Stream(device=device, priority=-1)
             self._streams[device] = s
         return s
+
+
+def _mark_ready(state: B200HookState, buf: torch.Tensor):
+    if state.timeline is None or not buf.is_cuda:
+        return None
+    ev = torch.cuda.Event(enable_timing=True)
+    ev.record(torch.cuda.current_stream(buf.device))
+    return ev
+
+
+def _mark_done(state: B200HookState, buf: torch.Tensor, ready, stream) -> None:
+    if ready is None:
+        return
+    ev = torch.cuda.Event(enable_timing=True)
+    ev.record(stream)
+    state.timeline.append((ready, ev, buf.numel() * buf.element_size()))
 
 
 def _launch(state: B200HookState, buf: torch.Tensor, body: Callable[[], "dist.Work"]) -> "dist.Work":
@@ -196,6 +216,7 @@ def b200_nvlink_allreduce_hook(state: B200NvlinkState, bucket: dist.GradBucket) 
     state.buckets_seen += 1
     state.bytes_reduced += n * 2
     off, padded = state.carve(bucket.index(), n)
+    ready = _mark_ready(state, buf)
     hdl = state.handle
     view = _alias_bf16(state.arena.data_ptr() + 2 * off, n, buf.device)  # same memory as arena[off:off+n]
     lib = _cabi.load()
@@ -216,6 +237,7 @@ def b200_nvlink_allreduce_hook(state: B200NvlinkState, bucket: dist.GradBucket) 
                         "b200sft_allreduce_scale_bf16_p2p")
         ops.STATS.kernel_launches += 1
         hdl.barrier(channel=0)                      # every rank's slice of the result has landed everywhere
+        _mark_done(state, buf, ready, side)
         fut = torch.futures.Future(devices=[buf.device])
         fut.set_result(view)
     return fut

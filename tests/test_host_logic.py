@@ -158,3 +158,16 @@ def test_patched_model_saves_and_reloads_as_stock(tiny, tmp_path):
     # (logits agree to bf16 resolution only: the fixture's .to(bfloat16) also cast the rotary inv_freq buffer,
     # which a fresh from_pretrained keeps in fp32 -- stock transformers behaviour, independent of the head swap)
     assert torch.allclose(again(input_ids=ids).logits.float(), before.float(), atol=2e-2)
+
+
+def test_split_sizes_match_the_reference_run():
+    """2,845 QA rows -> 2,560 train / 285 validation, the sizes the reference reports for
+    train_test_split(test_size=0.1, seed=42) (training.py:164; docs/AIM_WORKFLOW.md:47-54)."""
+    from llm_fine_tune_distributed_b200.training import load_qa_rows, train_test_split
+
+    path = "/root/reference/data/qa_dataset.parquet"
+    rows = load_qa_rows(path) if os.path.exists(path) else [{"full-question": str(i), "answer": "a"} for i in range(2845)]
+    assert len(rows) == 2845 and set(rows[0]) == {"full-question", "answer"}
+    train, val = train_test_split(rows, 0.1, 42)
+    assert (len(train), len(val)) == (2560, 285)
+    assert train_test_split(rows, 0.1, 42)[1] == val          # deterministic in the seed

@@ -430,6 +430,8 @@ def run_b200(args) -> dict:
             "avg_launch_ms": round(fwd_ms, 4),
             "frac_of_burst_peak": round(achieved / peaks["burst"], 4),
             "ncu_tensor_pipe_active_pct": tensor_pct,  # from the committed ncu --set full capture, not measured live
+            "note": "timed inside the training step, so the denominator is the sustained cuBLAS figure; the step is not "
+                    "tensor-bound end to end, the SMs hold burst clocks (see clocks.sm_mhz) and the kernel runs above it",
         },
         "flce_bwd": {"avg_call_ms": round(bwd_ms, 4), "algorithmic_flops_per_call": 4.0 * N * H * V,
                      "achieved_tflops": round(4.0 * N * H * V / (bwd_ms / 1e3) / 1e12, 1),

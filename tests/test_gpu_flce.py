@@ -313,3 +313,22 @@ def test_flce_backward_skips_unneeded_gradients(cuda_device):
         ops.fused_linear_cross_entropy(x, w1, lab, denom, skip_ignored_rows=skip).backward()      # only the head trains
         assert torch.allclose(w1.grad.float(), wg.grad.float(), rtol=2.0 ** -7, atol=1e-7)
         assert ops.STATS.kernel_launches < launches_dx_only + 2
+
+
+@pytest.mark.parametrize("gain", [30.0, 300.0])
+def test_flce_extreme_logits_stay_finite_and_accurate(cuda_device, gain):
+    """Logits in the hundreds / thousands (peaked softmax, exp underflow everywhere but the maximum):
+    the online max/sum-exp must neither overflow nor lose the target term."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    x, w, labels = _case(384, 128, 4096, 0.2, seed=41, device=cuda_device)
+    x = (x.float() * gain).to(torch.bfloat16)
+    lab = labels.to(torch.int32)
+    denom = torch.tensor(int((labels != -100).sum()), dtype=torch.int64, device=cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    loss = ops.fused_linear_cross_entropy(xg, wg, lab, denom, flags=ops.FLAG_ROUND_LOGITS_BF16)
+    loss.backward()
+    ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, float(denom))
+    assert torch.isfinite(loss) and torch.isfinite(xg.grad.float()).all() and torch.isfinite(wg.grad.float()).all()
+    assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
+    assert _cos(xg.grad, ref_dx) >= 0.999 and _cos(wg.grad, ref_dw) >= 0.999

@@ -55,3 +55,38 @@ def test_full_size_parity_and_properties(cuda_device, case, skip):
     xg2, wg2 = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
     (ops.fused_linear_cross_entropy(xg2, wg2, labels.to(torch.int32), n_items, skip_ignored_rows=skip) * 4.0).backward()
     assert torch.equal(xg2.grad, xg.grad * 4) and torch.equal(wg2.grad, wg.grad * 4)
+
+
+def test_largest_config_properties(cuda_device):
+    """BASELINE config 4's largest point, 65,536 tokens (torch's own path needs ~94 GB there): no oracle
+    at this size, so check the size-independent properties -- finite loss near ln(V) for random
+    weights, ignored rows exactly zero, sum_v dW[v,:] = 0, linearity in the upstream gradient, and
+    agreement of the compacted path with the dense one."""
+    import math
+
+    from llm_fine_tune_distributed_b200 import ops
+
+    Nbig = 65536
+    x = torch.randn(Nbig, H, generator=torch.Generator().manual_seed(5)).to(torch.bfloat16).to(cuda_device)
+    w = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(torch.bfloat16).to(cuda_device)
+    labels = torch.randint(0, V, (Nbig,), generator=torch.Generator().manual_seed(6))
+    labels[torch.rand(Nbig, generator=torch.Generator().manual_seed(7)) < 0.5] = -100
+    labels = labels.to(cuda_device)
+    lab = labels.to(torch.int32)
+    n_items = torch.tensor(int((labels != -100).sum()), dtype=torch.int64, device=cuda_device)
+    grads = {}
+    for skip, gain in ((False, 1.0), (True, 1.0), (True, 2.0)):
+        xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        loss = ops.fused_linear_cross_entropy(xg, wg, lab, n_items, skip_ignored_rows=skip)
+        (loss * gain).backward()
+        grads[(skip, gain)] = (loss.item(), xg.grad, wg.grad)
+        del xg, wg
+    l0, dx0, dw0 = grads[(False, 1.0)]
+    l1, dx1, dw1 = grads[(True, 1.0)]
+    _, dx2, dw2 = grads[(True, 2.0)]
+    assert math.isfinite(l0) and abs(l0 - math.log(V)) < 1.0          # random head: loss ~ ln(128256) = 11.76 (+ spread)
+    assert abs(l0 - l1) <= 1e-5 * abs(l0)
+    assert torch.count_nonzero(dx0[labels == -100]) == 0 and torch.count_nonzero(dx1[labels == -100]) == 0
+    assert _cos(dx0, dx1) > 0.99999 and _cos(dw0, dw1) > 0.9999
+    assert float(dw0.float().sum(dim=0).abs().max()) <= 4.0 * float(dw0.float().abs().max())   # ~0 vs 128k summed rows
+    assert torch.equal(dx2, dx1 * 2) and torch.equal(dw2, dw1 * 2)

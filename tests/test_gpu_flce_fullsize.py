@@ -90,3 +90,24 @@ def test_largest_config_properties(cuda_device):
     assert _cos(dx0, dx1) > 0.99999 and _cos(dw0, dw1) > 0.9999
     assert float(dw0.float().sum(dim=0).abs().max()) <= 4.0 * float(dw0.float().abs().max())   # ~0 vs 128k summed rows
     assert torch.equal(dx2, dx1 * 2) and torch.equal(dw2, dw1 * 2)
+
+
+@pytest.mark.parametrize("Nn,Hh,Vv", [(1024, 4096, 151936), (768, 1024, 50264)])
+def test_other_model_shapes(cuda_device, Nn, Hh, Vv):
+    """Not SmolLM3-specific: a wider hidden size and vocabularies that are not multiples of the 256-column
+    tile (151,936 = 593.5 tiles; 50,264 = 196.3 tiles) against the oracle."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    g = torch.Generator().manual_seed(Nn + Vv)
+    x = torch.randn(Nn, Hh, generator=g).to(torch.bfloat16).to(cuda_device)
+    w = (torch.randn(Vv, Hh, generator=g) * 0.02).to(torch.bfloat16).to(cuda_device)
+    labels = torch.randint(0, Vv, (Nn,), generator=g)
+    labels[torch.rand(Nn, generator=g) < 0.3] = -100
+    labels[0] = Vv - 1                                   # a target in the ragged last tile
+    labels = labels.to(cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    loss = ops.fused_linear_cross_entropy(xg, wg, labels.to(torch.int32), None, skip_ignored_rows=True)
+    loss.backward()
+    ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads(x, w, labels, None)
+    assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
+    assert _cos(xg.grad, ref_dx) >= 0.999 and _cos(wg.grad, ref_dw) >= 0.999

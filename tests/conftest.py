@@ -12,6 +12,17 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200, sm_100a); run with -m gpu")
 
 
+def pytest_sessionstart(session):
+    """Make sure libb200sft.so exists and is current before any test touches it (nvcc is present both in the
+    build container and on the GPU box; a missing compiler is reported by the tests that need the library)."""
+    try:
+        from llm_fine_tune_distributed_b200 import build
+
+        build.build()
+    except Exception as e:  # pragma: no cover - surfaced by _cabi.load() in the tests
+        print(f"[conftest] could not build libb200sft.so: {e}", file=sys.stderr)
+
+
 @pytest.fixture(scope="session")
 def cuda_device():
     import torch

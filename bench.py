@@ -195,7 +195,6 @@ def window_tokens(window) -> tuple:
 # this repository's arm
 # ------------------------------------------------------------------------------------------
 def run_b200(args) -> dict:
-    from llm_fine_tune_distributed_b200 import ops
     from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, B200NvlinkState, b200_allreduce_hook,
                                                           b200_nvlink_allreduce_hook)
     from llm_fine_tune_distributed_b200.loss import FusedCELossMixin, install_fused_head
@@ -208,6 +207,15 @@ def run_b200(args) -> dict:
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    from llm_fine_tune_distributed_b200 import _cabi, build as _build
+
+    if not _cabi.LIB_PATH.exists():  # normally prebuilt by __graft_entry__.build(); one rank compiles if it is not
+        if local_rank == 0:
+            _build.build()
+        if world > 1:
+            dist.barrier()
+    from llm_fine_tune_distributed_b200 import ops
+
     B, T, GA = args.batch, args.seq, args.ga
     attn = pick_attn() if args.attn == "auto" else args.attn
     model = build_model(dev, attn, args.layers)

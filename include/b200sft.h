@@ -159,6 +159,9 @@ int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels
  *   n_rows_dev  as in b200sft_flce_fwd (compacted inputs; dx is then compact too)
  */
 size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols);
+/* Number of kernels one b200sft_flce_bwd call launches for this shape (per vocabulary slab: dlogits,
+ * dX, dW GEMMs; plus the split-K combine) -- bookkeeping for benchmarks; no reference counterpart. */
+int b200sft_flce_bwd_launch_count(int N, int H, int V, int chunk_cols, int need_dx, int need_dw);
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse,
                      const float* grad_out, int N, int H, int V, int ignore_index, float scale,
                      int denom_mode, const int64_t* denom, uint32_t flags, int chunk_cols,

@@ -36,6 +36,7 @@ SIGNATURES = {
     "b200sft_flce_fwd_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
                                          c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200sft_flce_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200sft_flce_bwd_launch_count": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "b200sft_flce_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                  c_float, c_int, c_void_p, c_uint32, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_size_t, c_void_p]),

@@ -869,6 +869,14 @@ size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols) {
   return b;
 }
 
+int b200sft_flce_bwd_launch_count(int N, int H, int V, int chunk_cols, int need_dx, int need_dw) {
+  if (N <= 0 || H <= 0 || V <= 0) return 0;
+  const int slab = resolve_slab_cols(N, V, chunk_cols);
+  const int num_slabs = (V + slab - 1) / slab;
+  const int combine = (need_dx && dx_max_k_splits(N, H) > 1) ? 1 : 0;
+  return num_slabs * (1 + (need_dx ? 1 : 0) + (need_dw ? 1 : 0)) + combine;
+}
+
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse, const float* grad_out,
                      int N, int H, int V, int ignore_index, float scale, int denom_mode, const int64_t* denom,
                      uint32_t flags, int chunk_cols, const int32_t* n_rows_dev, void* dx, void* dw, void* workspace,

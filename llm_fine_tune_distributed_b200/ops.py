@@ -50,17 +50,6 @@ class _Stats:
 STATS = _Stats()
 
 
-def _bwd_num_slabs(N: int, V: int, chunk_cols: int) -> int:
-    """Mirror of resolve_slab_cols() in csrc/flce.cu -- used only to count kernel launches."""
-    v_up = (V + 255) // 256 * 256
-    cmax = (chunk_cols + 255) // 256 * 256 if chunk_cols > 0 else max(((1 << 30) // (2 * N)) // 256 * 256, 256)
-    if cmax >= v_up:
-        return 1
-    slabs = (v_up + cmax - 1) // cmax
-    c = ((v_up + slabs - 1) // slabs + 255) // 256 * 256
-    return (V + c - 1) // c
-
-
 __all__ = [
     "label_prep", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
     "scale_cast_f32_to_bf16", "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX",
@@ -204,8 +193,7 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
                                    ignore_index, float(scale), mode, _ptr(denom), flags, chunk_cols, _ptr(n_rows),
                                    _ptr(dx), _ptr(dw), _ptr(ws), ws_bytes, _stream_ptr(x)), "b200sft_flce_bwd")
         STATS.end(ev, x.device)
-        STATS.kernel_launches += (1 + int(need_dx) + int(need_dw)) * _bwd_num_slabs(N, V, chunk_cols) + int(need_dx)
-        # per vocabulary slab: dlogits GEMM + dX GEMM + dW GEMM; plus the split-K combine for dX (when split)
+        STATS.kernel_launches += lib.b200sft_flce_bwd_launch_count(N, H, V, chunk_cols, int(need_dx), int(need_dw))
     return dx, dw
 
 

@@ -94,6 +94,7 @@ class SFTSettings:
             learning_rate=lr * world_size if world_size > 1 else lr,  # training.py:263
             num_train_epochs=float(os.getenv("EPOCHS", "4")),
             max_steps=int(os.getenv("MAX_STEPS", "-1")),
+            eval_steps=int(os.getenv("EVAL_STEPS", "10")),
             gradient_accumulation_steps=int(os.getenv("GRAD_ACCUM", "4")),
             ddp_backend="nccl" if world_size > 1 else None,
             local_rank=local_rank,
@@ -343,6 +344,8 @@ class MiniSFTTrainer(FusedCELossMixin):
         self.lr_scheduler = torch.optim.lr_scheduler.LambdaLR(
             self.optimizer, lambda s: max(0.0, 1.0 - s / max(self.max_steps, 1)))  # linear decay, Trainer default
         self.global_step = 0
+        self.best_eval_loss: Optional[float] = None
+        self.best_step: Optional[int] = None
 
     # -- pieces of _inner_training_loop ------------------------------------------------------
     def get_batch_samples(self, it: Iterator, n: int) -> tuple:
@@ -379,6 +382,41 @@ class MiniSFTTrainer(FusedCELossMixin):
         for cb in self.callbacks:
             if hasattr(cb, "on_log"):
                 cb.on_log(logs)
+
+    @torch.no_grad()
+    def evaluate(self) -> Dict[str, float]:
+        """``Trainer.evaluate`` for this configuration (eval_strategy="steps", eval_steps=10,
+        metric_for_best_model="eval_loss": training.py:270-275): the model loss of every validation
+        batch -- same fused path, no_grad, ``num_items_in_batch`` None so each batch is a mean over
+        its valid tokens -- averaged over batches and ranks."""
+        if self.eval_batches is None or len(self.eval_batches) == 0:
+            return {}
+        was_training = self.model_wrapped.training
+        self.model.eval()
+        t0 = time.time()
+        total = torch.zeros((), device=self.device)
+        n = 0
+        for inputs in self.eval_batches.epoch(0):
+            inputs = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in inputs.items()}
+            if self.loss_impl is not None:
+                total += self.loss_impl(self.model, inputs, None).float()
+            else:
+                total += self.compute_loss(self.model, inputs).float()   # unwrapped model, as prediction_step uses it
+            n += 1
+        if self.world > 1:
+            dist.all_reduce(total, op=dist.ReduceOp.SUM)
+            total /= self.world
+        self.model.train(was_training)
+        dt = time.time() - t0
+        samples = n * self.eval_batches.bs * self.world
+        logs = {"eval_loss": float(total) / max(n, 1), "eval_runtime": round(dt, 4),
+                "eval_samples_per_second": round(samples / dt, 3) if dt > 0 else 0.0,
+                "eval_steps_per_second": round(n / dt, 3) if dt > 0 else 0.0,
+                "epoch": round(self.global_step / max(len(self.train_batches) // self.args.gradient_accumulation_steps, 1), 4)}
+        if self.best_eval_loss is None or logs["eval_loss"] < self.best_eval_loss:   # greater_is_better=False
+            self.best_eval_loss, self.best_step = logs["eval_loss"], self.global_step
+        self._log(logs)
+        return logs
 
     def train(self) -> TrainResult:
         args = self.args
@@ -419,6 +457,8 @@ class MiniSFTTrainer(FusedCELossMixin):
                             "epoch": round(self.global_step / max(len(self.train_batches) // ga, 1), 4)}
                     logged_loss, last_logged_step = total, self.global_step
                     self._log(logs)
+                if args.eval_steps > 0 and self.global_step % args.eval_steps == 0:
+                    self.evaluate()
             epoch += 1
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)

@@ -25,6 +25,7 @@ def _write_parquet(path, n=96):
 def _env(tmp_path, **extra):
     env = dict(os.environ)
     env.update(RANDOM_INIT="1", MODEL_CONFIG="tiny", ATTN_IMPL="sdpa", MAX_STEPS="3", BATCH_SIZE="4", GRAD_ACCUM="2",
+               EVAL_STEPS="2",
                EPOCHS="1", LEARNING_RATE="1e-4", DATASET_PATH=str(tmp_path / "qa.parquet"),
                OUTPUT_DIR=str(tmp_path / "out"), PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
     env.update(extra)
@@ -38,8 +39,12 @@ def _check(tmp_path, world):
     assert summary["world_size"] == world and summary["distributed_training"] == (world > 1)
     assert summary["training_samples"] + summary["validation_samples"] == 96
     assert summary["trainable_params"] <= summary["total_params"]
-    # logging_first_step=True, logging_steps=2 (training.py:266-267): 3 optimizer steps log at steps 1 and 2
-    assert len(history) == 2 and all(8.0 < h["loss"] < 16.0 and "perplexity" in h for h in history)
+    # logging_first_step=True, logging_steps=2 (training.py:266-267): 3 optimizer steps log at steps 1 and 2;
+    # EVAL_STEPS=2 adds one evaluation entry after step 2 (eval_loss + eval_perplexity, training.py:224-234)
+    train_logs = [h for h in history if "loss" in h]
+    eval_logs = [h for h in history if "eval_loss" in h]
+    assert len(train_logs) == 2 and all(8.0 < h["loss"] < 16.0 and "perplexity" in h for h in train_logs)
+    assert len(eval_logs) == 1 and 8.0 < eval_logs[0]["eval_loss"] < 16.0 and "eval_perplexity" in eval_logs[0]
     assert os.path.isdir(out / "best_model") and os.listdir(out / "best_model")
 
 

@@ -560,7 +560,15 @@ def main() -> None:  # mirrors training.py:49-349
         except Exception as e:  # offline: fall through to random init of the same architecture
             print(f"could not load {MODEL_NAME} ({type(e).__name__}); using random-init weights")
     if model is None:
-        model = make_model(os.getenv("MODEL_CONFIG", "3b"), device, os.getenv("ATTN_IMPL"))
+        attn = os.getenv("ATTN_IMPL")
+        if attn is None:  # the reference loads with attn_implementation="flash_attention_2" (training.py:101)
+            try:
+                import flash_attn  # noqa: F401
+
+                attn = "flash_attention_2"
+            except Exception:
+                attn = None
+        model = make_model(os.getenv("MODEL_CONFIG", "3b"), device, attn)
     if tokenizer is None:
         tokenizer = ByteChatTokenizer(model.config.vocab_size)
     model = model.to(device)

@@ -52,6 +52,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--chunk-cols", type=int, default=0)
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--cpu-tokens", type=int, default=0,
+                    help="also time the reference head + CE forward/backward on the host cores at this many tokens "
+                         "(oracle.lm_head_ce_with_grads: F.linear -> .float() -> F.cross_entropy + autograd, bf16)")
     ap.add_argument("--kernel-times", action="store_true", help="also print per-kernel device times (torch.profiler)")
     ap.add_argument("--skip-ignored", action="store_true", help="compact away ignore_index rows first (valid-row compaction)")
     args = ap.parse_args()
@@ -61,6 +64,22 @@ def main():
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     gw = torch.Generator(device="cpu").manual_seed(1)
     w = (torch.randn(V, H, generator=gw) * 0.02).to(torch.bfloat16).to(dev)
+    if args.cpu_tokens > 0:
+        import time
+
+        from oracle import sft_oracle as oracle
+
+        n = args.cpu_tokens
+        xc = torch.randn(n, H, generator=torch.Generator().manual_seed(0)).to(torch.bfloat16)
+        wc = w.cpu()
+        lc = torch.randint(0, V, (n,), generator=torch.Generator().manual_seed(2))
+        oracle.lm_head_ce_with_grads(xc[:64], wc, lc[:64], 64.0)      # warm the thread pool
+        t0 = time.perf_counter()
+        oracle.lm_head_ce_with_grads(xc, wc, lc, float(n))
+        dt = time.perf_counter() - t0
+        print(json.dumps({"cpu_reference_head_ce": {"tokens": n, "seconds_fwd_bwd": round(dt, 3),
+                                                    "tflops_6NHV": round(6.0 * n * H * V / dt / 1e12, 3),
+                                                    "threads": torch.get_num_threads(), "os_cpu_count": os.cpu_count()}}), flush=True)
     for N in args.tokens:
         gx = torch.Generator(device="cpu").manual_seed(0)
         x = torch.randn(N, H, generator=gx).to(torch.bfloat16).to(dev)

@@ -105,7 +105,7 @@ def _check_flce_inputs(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -
         raise ValueError("x and w must be bfloat16")
     if labels.dtype != torch.int32:
         raise ValueError("labels must be int32 (use label_prep)")
-    if x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1]:
+    if x.dim() != 2 or w.dim() != 2 or x.shape[-1] != w.shape[-1]:
         raise ValueError(f"x [N,H] / w [V,H] shape mismatch: {tuple(x.shape)} vs {tuple(w.shape)}")
     if labels.dim() != 1 or labels.shape[0] != x.shape[0]:
         raise ValueError("labels must be [N]")
@@ -138,6 +138,11 @@ def flce_forward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, scale: 
         if n_rows.dtype != torch.int32 or n_rows.numel() != 1:
             raise ValueError("n_rows must be a single int32 on the device")
     mode = DENOM_DEVICE if denom is not None else (DENOM_VALID if reduction_mean else DENOM_NONE)
+    if N == 0:  # empty batch: nothing to launch.  torch: sum-reduction 0, mean-reduction nan (0/0)
+        loss = torch.full((), float("nan") if reduction_mean else 0.0, dtype=torch.float32, device=x.device)
+        out = (loss, torch.empty(0, dtype=torch.float32, device=x.device), torch.zeros((), dtype=torch.int64, device=x.device))
+        return (*out, torch.zeros((), dtype=torch.int64, device=x.device),
+                torch.zeros((), dtype=torch.float32, device=x.device)) if with_stats else out
     lib = _cabi.load()
     with torch.cuda.device(x.device):
         loss = torch.empty((), dtype=torch.float32, device=x.device)
@@ -180,6 +185,8 @@ def flce_backward(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, lse: t
         raise ValueError("lse must be float32 [N]")
     grad_out = grad_out.to(torch.float32).reshape(()).contiguous()
     mode = DENOM_DEVICE if denom is not None else DENOM_NONE
+    if N == 0:  # empty batch: no rows, zero weight gradient
+        return (torch.empty_like(x) if need_dx else None), (torch.zeros_like(w) if need_dw else None)
     lib = _cabi.load()
     with torch.cuda.device(x.device):
         ws_bytes = lib.b200sft_flce_bwd_workspace_bytes(N, H, V, chunk_cols)
@@ -207,6 +214,9 @@ def compact_rows(x: torch.Tensor, labels: torch.Tensor, ignore_index: int = IGNO
     if not (x.is_contiguous() and labels.is_contiguous()):
         raise ValueError("x and labels must be contiguous")
     N, H = x.shape
+    if N == 0:
+        z = torch.empty(0, dtype=torch.int32, device=x.device)
+        return x, labels, z, z.clone(), torch.zeros((), dtype=torch.int32, device=x.device)
     lib = _cabi.load()
     with torch.cuda.device(x.device):
         xc = torch.empty_like(x)
@@ -224,6 +234,8 @@ def scatter_rows(dxc: torch.Tensor, pos: torch.Tensor) -> torch.Tensor:
     """dx[r] = dxc[pos[r]] if pos[r] >= 0 else 0 (inverse of :func:`compact_rows` for gradients)."""
     _require_cuda(dxc, pos)
     N, H = dxc.shape
+    if N == 0:
+        return dxc
     lib = _cabi.load()
     with torch.cuda.device(dxc.device):
         dx = torch.empty_like(dxc)

@@ -332,3 +332,22 @@ def test_flce_extreme_logits_stay_finite_and_accurate(cuda_device, gain):
     assert torch.isfinite(loss) and torch.isfinite(xg.grad.float()).all() and torch.isfinite(wg.grad.float()).all()
     assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
     assert _cos(xg.grad, ref_dx) >= 0.999 and _cos(wg.grad, ref_dw) >= 0.999
+
+
+@pytest.mark.parametrize("skip", [False, True])
+def test_flce_empty_batch_matches_torch(cuda_device, skip):
+    """Zero rows: torch gives loss 0 for reduction="sum" (nan for "mean"), an empty dX and a zero dW."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    H, V = 64, 512
+    x = torch.empty(0, H, dtype=torch.bfloat16, device=cuda_device, requires_grad=True)
+    w = torch.randn(V, H, device=cuda_device).to(torch.bfloat16).requires_grad_(True)
+    labels = torch.empty(0, dtype=torch.int32, device=cuda_device)
+    denom = torch.tensor(5, dtype=torch.int64, device=cuda_device)
+    loss = ops.fused_linear_cross_entropy(x, w, labels, denom, skip_ignored_rows=skip)
+    loss.backward()
+    ref = oracle.lm_head_ce(x.detach(), w.detach(), labels.long(), 5.0)
+    assert loss.item() == ref.item() == 0.0
+    assert x.grad.shape == (0, H) and torch.count_nonzero(w.grad) == 0
+    mean = ops.fused_linear_cross_entropy(x.detach(), w.detach(), labels, None, skip_ignored_rows=skip)
+    assert torch.isnan(mean) and torch.isnan(oracle.lm_head_ce(x.detach(), w.detach(), labels.long(), None))

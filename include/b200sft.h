@@ -58,6 +58,30 @@ int b200sft_set_cta_group(int cta_group);
 int b200sft_label_prep(const int64_t* labels, int B, int T, int64_t ignore_index, int32_t* shifted,
                        int64_t* counts, void* stream);
 
+/* The whole label front-end in one launch: what the collators do to the labels on the host, the
+ * shift, both counts and the live-row compaction list that b200sft_gather_rows / flce consume.
+ * The unshifted label of token i is
+ *   (labels ? labels : input_ids)[i]          labels = input_ids copy: data_collator.py:1428
+ *   -> ignore_index where attention_mask[i] == 0     padding (labels padded with -100)
+ *   -> ignore_index where completion_mask[i] == 0    prompt tokens under completion-only loss
+ *                                                    [TRL collator, not on disk]
+ *   -> ignore_index where position_ids[i] == 0       first token of a packed sequence, the separator
+ *                                                    of DataCollatorWithFlattening
+ *                                                    (SP/transformers/data/data_collator.py:1426-1428)
+ * followed by the shift and counts of b200sft_label_prep.  Every mask pointer may be NULL (= no such
+ * mask); all are [B,T] int64.
+ *   labels_out [B,T] int64 out or NULL: the unshifted labels (what inputs["labels"] would hold)
+ *   shifted    [B*T] int32 out;  counts [2] int64 out (as b200sft_label_prep)
+ *   row_index, labels_c, pos [B*T] int32, n_live int32 scalar: outputs as b200sft_compact_rows, or
+ *   all four NULL to skip the compaction.  B*T < 2^31.  Bit-exact integer work; reached from
+ *   training.py:300 (collator -> compute_loss).
+ */
+int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, const int64_t* attention_mask,
+                           const int64_t* completion_mask, const int64_t* position_ids, int B, int T,
+                           int64_t ignore_index, int64_t* labels_out, int32_t* shifted, int64_t* counts,
+                           int32_t* row_index, int32_t* labels_c, int32_t* pos, int32_t* n_live,
+                           void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Fused LM-head + masked cross-entropy, forward.  Replaces, for training.py:300's step,
  *   logits = lm_head(hidden)            SP/transformers/models/smollm3/modeling_smollm3.py:504
@@ -110,6 +134,10 @@ int b200sft_flce_fwd_stats(const void* x, const void* w, const int32_t* labels, 
  */
 int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int ignore_index, void* xc,
                          int32_t* labels_c, int32_t* row_index, int32_t* pos, int32_t* n_live, void* stream);
+/*   The gather half alone, for a compaction list made by b200sft_label_frontend:
+ *   xc[j,:] = x[row_index[j],:] for j < *n_live, zero rows up to the next 128-row boundary. */
+int b200sft_gather_rows(const void* x, const int32_t* row_index, const int32_t* n_live, int N, int H, void* xc,
+                        void* stream);
 /*   dx[r,:] = dxc[pos[r],:] when pos[r] >= 0, else 0 (every row of dx is written). */
 int b200sft_scatter_rows(const void* dxc, const int32_t* pos, int N, int H, void* dx, void* stream);
 

@@ -15,7 +15,9 @@ from .ops import (  # noqa: F401
     flce_backward,
     flce_forward,
     fused_linear_cross_entropy,
+    gather_rows,
     gemm_bf16,
+    label_frontend,
     label_prep,
     scale_,
     scale_cast_f32_to_bf16,

@@ -81,6 +81,109 @@ __global__ void label_prep_kernel(const int64_t* __restrict__ labels, int B, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// label front-end, whole: collator masks + shift + both counts + live-row compaction, ONE launch
+// ---------------------------------------------------------------------------------------------
+// The unshifted label of token i is what the collators would have written on the host:
+//   src[i] (labels, or input_ids when the collator copies them), replaced by ignore_index where
+//   attention_mask[i] == 0 (padding), completion_mask[i] == 0 (prompt tokens under
+//   completion-only loss) or position_ids[i] == 0 (first token of a packed sequence -- the
+//   separator DataCollatorWithFlattening writes, SP/transformers/data/data_collator.py:1426-1428).
+// One 1024-thread block: each warp owns one contiguous run and walks it 32 tokens at a time
+// (coalesced), so the stable compaction is a ballot + popc per step and one 32-entry scan over
+// the warp totals.  Nothing needs zeroing beforehand and nothing is accumulated with atomics.
+struct LabelSources {
+  const int64_t* src;
+  const int64_t* attention_mask;
+  const int64_t* completion_mask;
+  const int64_t* position_ids;
+  int64_t ignore_index;
+  __device__ __forceinline__ int64_t at(size_t i) const {
+    int64_t v = src[i];
+    if (attention_mask != nullptr && attention_mask[i] == 0) v = ignore_index;
+    if (completion_mask != nullptr && completion_mask[i] == 0) v = ignore_index;
+    if (position_ids != nullptr && position_ids[i] == 0) v = ignore_index;
+    return v;
+  }
+};
+
+constexpr int FRONTEND_THREADS = 1024;
+
+__global__ void __launch_bounds__(FRONTEND_THREADS)
+label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ labels_out, int32_t* __restrict__ shifted,
+                      int64_t* __restrict__ counts, int32_t* __restrict__ row_index, int32_t* __restrict__ labels_c,
+                      int32_t* __restrict__ pos, int32_t* __restrict__ n_live) {
+  __shared__ unsigned int s_live[32], s_unshifted[32], s_base[33];
+  const size_t total = static_cast<size_t>(B) * T;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned int lt_mask = (1u << lane) - 1u;
+  const size_t per = ((total + 31) / 32 + 31) / 32 * 32;  // tokens per warp, a multiple of 32
+  const size_t lo = min(static_cast<size_t>(warp) * per, total), hi = min(lo + per, total);
+  const int32_t ignore32 = static_cast<int32_t>(in.ignore_index);
+
+  // pass 1: labels, shifted labels, per-warp counts
+  unsigned int live = 0, unshifted = 0;
+  for (size_t base = lo; base < hi; base += 32) {
+    const size_t i = base + lane;
+    bool is_live = false, is_unshifted = false;
+    if (i < hi) {
+      const int64_t cur = in.at(i);
+      const int t = static_cast<int>(i % T);
+      const int64_t nxt = (t + 1 < T) ? in.at(i + 1) : in.ignore_index;
+      if (labels_out != nullptr) labels_out[i] = cur;
+      shifted[i] = static_cast<int32_t>(nxt);
+      is_unshifted = cur != in.ignore_index;
+      is_live = nxt != in.ignore_index;
+    }
+    live += __popc(__ballot_sync(0xffffffffu, is_live));
+    unshifted += __popc(__ballot_sync(0xffffffffu, is_unshifted));
+  }
+  if (lane == 0) {
+    s_live[warp] = live;
+    s_unshifted[warp] = unshifted;
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan of the 32 warp totals
+    unsigned int v = s_live[lane], u = s_unshifted[lane];
+    unsigned int incl = v;
+    for (int off = 1; off < 32; off <<= 1) {
+      const unsigned int o = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += o;
+      u += __shfl_xor_sync(0xffffffffu, u, off);
+    }
+    s_base[lane] = incl - v;
+    if (lane == 31) s_base[32] = incl;
+    if (lane == 0) counts[0] = static_cast<int64_t>(u);
+  }
+  __syncthreads();
+  const unsigned int n_total = s_base[32];
+  if (threadIdx.x == 0) {
+    counts[1] = static_cast<int64_t>(n_total);
+    if (n_live != nullptr) *n_live = static_cast<int32_t>(n_total);
+  }
+  if (row_index == nullptr) return;
+
+  // pass 2: stable compaction (each thread re-reads the shifted labels it wrote itself)
+  unsigned int at = s_base[warp];
+  for (size_t base = lo; base < hi; base += 32) {
+    const size_t i = base + lane;
+    int32_t l = ignore32;
+    if (i < hi) l = shifted[i];
+    const bool is_live = (i < hi) && l != ignore32;
+    const unsigned int ballot = __ballot_sync(0xffffffffu, is_live);
+    if (is_live) {
+      const unsigned int j = at + __popc(ballot & lt_mask);
+      row_index[j] = static_cast<int32_t>(i);
+      labels_c[j] = l;
+      pos[i] = static_cast<int32_t>(j);
+    } else if (i < hi) {
+      pos[i] = -1;
+    }
+    at += __popc(ballot);
+  }
+  for (size_t j = n_total + threadIdx.x; j < total; j += blockDim.x) labels_c[j] = ignore32;  // dead tail
+}
+
+// ---------------------------------------------------------------------------------------------
 // scale / cast (gradient buckets)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t scale_bf16x2(uint32_t v, float s) {
@@ -243,6 +346,32 @@ int b200sft_label_prep(const int64_t* labels, int B, int T, int64_t ignore_index
   const int threads = 256;
   label_prep_kernel<<<grid_for(total, threads, 8), threads, 0, stream>>>(
       labels, B, T, ignore_index, shifted, reinterpret_cast<unsigned long long*>(counts));
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
+int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, const int64_t* attention_mask,
+                           const int64_t* completion_mask, const int64_t* position_ids, int B, int T,
+                           int64_t ignore_index, int64_t* labels_out, int32_t* shifted, int64_t* counts,
+                           int32_t* row_index, int32_t* labels_c, int32_t* pos, int32_t* n_live, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (B < 0 || T < 0) return fail(B200SFT_ERR_INVALID, "negative label shape %d x %d", B, T);
+  if (!counts) return fail(B200SFT_ERR_INVALID, "null counts pointer");
+  const size_t total = static_cast<size_t>(B) * T;
+  if (total > static_cast<size_t>(INT32_MAX)) return fail(B200SFT_ERR_INVALID, "B*T = %zu exceeds int32 row indices", total);
+  const int64_t* src = labels ? labels : input_ids;
+  if (total == 0) {  // empty batch: counts and live count are zero
+    B200_CUDA_CHECK(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), stream));
+    if (n_live) B200_CUDA_CHECK(cudaMemsetAsync(n_live, 0, sizeof(int32_t), stream));
+    return B200SFT_OK;
+  }
+  if (!src || !shifted) return fail(B200SFT_ERR_INVALID, "null label source or shifted output");
+  const bool compact = row_index || labels_c || pos || n_live;
+  if (compact && !(row_index && labels_c && pos && n_live))
+    return fail(B200SFT_ERR_INVALID, "compaction outputs must be all set or all null");
+  LabelSources in{src, attention_mask, completion_mask, position_ids, ignore_index};
+  label_frontend_kernel<<<1, FRONTEND_THREADS, 0, stream>>>(in, B, T, labels_out, shifted, counts, row_index, labels_c,
+                                                             pos, n_live);
   B200_CUDA_CHECK(cudaGetLastError());
   return B200SFT_OK;
 }

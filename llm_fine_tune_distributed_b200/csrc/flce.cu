@@ -846,6 +846,20 @@ int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int
   return B200SFT_OK;
 }
 
+int b200sft_gather_rows(const void* x, const int32_t* row_index, const int32_t* n_live, int N, int H, void* xc,
+                        void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (N <= 0 || H <= 0 || H % 8 != 0) return fail(B200SFT_ERR_INVALID, "gather_rows: bad shape N=%d H=%d", N, H);
+  if (!x || !row_index || !n_live || !xc) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  const int warps = 8;
+  int grid = (N + warps - 1) / warps;
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  gather_rows_kernel<<<grid, warps * 32, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), row_index, n_live, N, H,
+                                                       static_cast<__nv_bfloat16*>(xc));
+  B200_CUDA_CHECK(cudaGetLastError());
+  return B200SFT_OK;
+}
+
 int b200sft_scatter_rows(const void* dxc, const int32_t* pos, int N, int H, void* dx, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (N <= 0 || H <= 0 || H % 8 != 0) return fail(B200SFT_ERR_INVALID, "scatter_rows: bad shape N=%d H=%d", N, H);

@@ -47,6 +47,7 @@ class FusedLMHead(nn.Module):
         self.weight = linear.weight
         self.armed = False
         self.last_stats = None  # {"n_valid", "n_correct", "entropy_sum"} of the latest fused call (token_stats)
+        self.plan = None  # ops.LabelPlan made ahead of the forward (labels built on the device), else None
 
     def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
         if self.armed:
@@ -82,7 +83,8 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, sk
     def loss_function(logits, labels, vocab_size=None, **kwargs):
         if head.armed:
             out = fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_cols=chunk_cols,
-                                       skip_ignored_rows=skip_ignored_rows, return_stats=token_stats, **kwargs)
+                                       skip_ignored_rows=skip_ignored_rows, return_stats=token_stats,
+                                       plan=head.plan, **kwargs)
             if token_stats:
                 out, head.last_stats = out
             return out
@@ -95,36 +97,48 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, sk
 
 
 @contextlib.contextmanager
-def fused_head_armed(model: nn.Module):
-    """While active, ``model(**inputs, labels=...)`` computes its loss with the fused kernels."""
+def fused_head_armed(model: nn.Module, plan: Optional["ops.LabelPlan"] = None):
+    """While active, ``model(**inputs, labels=...)`` computes its loss with the fused kernels.
+    ``plan``: an :class:`ops.LabelPlan` already made for this batch's labels (reused, not rebuilt)."""
     head = _unwrap(model).lm_head
     if not isinstance(head, FusedLMHead):
         raise RuntimeError("call install_fused_head(model) first")
-    prev = head.armed
-    head.armed = True
+    prev = head.armed, head.plan
+    head.armed, head.plan = True, plan
     try:
         yield
     finally:
-        head.armed = prev
+        head.armed, head.plan = prev
 
 
 def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                          num_items_in_batch: Optional[Union[torch.Tensor, int]] = None,
                          ignore_index: int = -100, shift_labels: Optional[torch.Tensor] = None,
                          flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
-                         return_stats: bool = False, **_unused: Any):
+                         return_stats: bool = False, plan: Optional["ops.LabelPlan"] = None, **_unused: Any):
     """``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:45-67) on hidden states.
 
     Same arguments and meaning, except that the first argument holds ``[B,T,H]`` hidden states:
     labels are shifted left (or ``shift_labels`` used as given), flattened, and the loss is the
     sum over non-ignored positions divided by ``num_items_in_batch`` -- or the mean over local
-    non-ignored positions when that is None.
+    non-ignored positions when that is None.  ``plan``: the :class:`ops.LabelPlan` of ``labels`` when the
+    caller already ran the label front-end (labels built on the device); used as is.
     """
     if hidden_states.dim() == 2:
         hidden_states = hidden_states.unsqueeze(0)
     B, T, H = hidden_states.shape
-    if shift_labels is None:
-        shifted, _counts = ops.label_prep(labels.to(hidden_states.device).reshape(B, T), ignore_index)
+    if shift_labels is not None:
+        plan = None
+    if plan is not None:
+        if plan.shifted.numel() != B * T or plan.shifted.device != hidden_states.device:
+            raise ValueError("label plan does not belong to this batch")
+        if skip_ignored_rows and plan.row_index is None:
+            raise ValueError("label plan was made without the compaction list")
+        shifted = plan.shifted
+    elif shift_labels is None:  # one launch: shift, counts and the live-row list the head compacts with
+        plan = ops.label_frontend(labels=labels.to(hidden_states.device).reshape(B, T).contiguous(),
+                                  ignore_index=ignore_index, compact=skip_ignored_rows)
+        shifted = plan.shifted
     else:
         shifted = shift_labels.to(hidden_states.device).reshape(-1).to(torch.int32).contiguous()
     h2 = hidden_states.reshape(B * T, H)
@@ -133,7 +147,7 @@ def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labe
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     return ops.fused_linear_cross_entropy(h2.contiguous(), w.contiguous(), shifted, num_items_in_batch,
                                           ignore_index=ignore_index, flags=flags, chunk_cols=chunk_cols,
-                                          skip_ignored_rows=skip_ignored_rows, return_stats=return_stats)
+                                          skip_ignored_rows=skip_ignored_rows, return_stats=return_stats, plan=plan)
 
 
 class FusedCELossMixin:
@@ -191,7 +205,9 @@ class FusedCELossMixin:
         kwargs = {}
         if num_items_in_batch is not None and getattr(self, "model_accepts_loss_kwargs", True):
             kwargs["num_items_in_batch"] = num_items_in_batch
-        with fused_head_armed(model):
+        inputs = dict(inputs)
+        plan = inputs.pop("b200sft_plan", None)  # labels built on the device ahead of the forward
+        with fused_head_armed(model, plan):
             outputs = model(**{**inputs, **kwargs})
         if isinstance(outputs, dict) and "loss" not in outputs:
             raise ValueError(

@@ -8,7 +8,7 @@ There is no fallback: CPU tensors are rejected and a missing library raises.
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import NamedTuple, Optional, Tuple
 
 import torch
 
@@ -51,7 +51,7 @@ STATS = _Stats()
 
 
 __all__ = [
-    "label_prep", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
+    "label_prep", "label_frontend", "gather_rows", "LabelPlan", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
     "scale_cast_f32_to_bf16", "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX",
     "FLAG_ROUND_LOGITS_BF16",
 ]
@@ -99,6 +99,74 @@ def label_prep(labels: torch.Tensor, ignore_index: int = IGNORE_INDEX) -> Tuple[
 # --------------------------------------------------------------------------------------------
 # fused LM-head + cross-entropy
 # --------------------------------------------------------------------------------------------
+class LabelPlan(NamedTuple):
+    """Device outputs of :func:`label_frontend`."""
+    shifted: torch.Tensor            # [B*T] int32 shifted labels
+    counts: torch.Tensor             # [2] int64: non-ignored labels before / after the shift
+    labels: Optional[torch.Tensor]   # [B,T] int64 unshifted labels (when asked for)
+    row_index: Optional[torch.Tensor]  # compaction list (when asked for): original row of compact row j
+    labels_c: Optional[torch.Tensor]   # compacted labels, ignore_index past the live count
+    pos: Optional[torch.Tensor]        # compact position of each row, -1 if ignored
+    n_live: Optional[torch.Tensor]     # int32 scalar
+
+
+def label_frontend(input_ids: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None,
+                   attention_mask: Optional[torch.Tensor] = None, completion_mask: Optional[torch.Tensor] = None,
+                   position_ids: Optional[torch.Tensor] = None, ignore_index: int = IGNORE_INDEX,
+                   compact: bool = True, return_labels: bool = False) -> LabelPlan:
+    """Everything between the raw batch and the fused loss in ONE launch: the collator's masking
+    (padding, completion-only, packed-sequence separators -- SP/transformers/data/data_collator.py:1426-1428),
+    the ForCausalLMLoss shift (loss_utils.py:57-60), both valid counts (trainer.py:2136) and the
+    live-row list the fused head skips masked rows with.  All inputs int64 ``[B,T]`` on the device;
+    ``labels`` defaults to ``input_ids``; masks may be None."""
+    src = labels if labels is not None else input_ids
+    if src is None:
+        raise ValueError("need labels or input_ids")
+    given = [t for t in (input_ids, labels, attention_mask, completion_mask, position_ids) if t is not None]
+    _require_cuda(*given)
+    if src.dim() != 2:
+        raise ValueError("expected [B, T] inputs")
+    for t in given:
+        if t.dtype != torch.int64 or t.shape != src.shape or not t.is_contiguous():
+            raise ValueError("label front-end inputs must be contiguous int64 tensors of one [B, T] shape")
+    B, T = src.shape
+    lib = _cabi.load()
+    dev = src.device
+    with torch.cuda.device(dev):
+        shifted = torch.empty(B * T, dtype=torch.int32, device=dev)
+        counts = torch.empty(2, dtype=torch.int64, device=dev)
+        labels_out = torch.empty(B, T, dtype=torch.int64, device=dev) if return_labels else None
+        row_index = labels_c = pos = n_live = None
+        if compact:
+            row_index, labels_c, pos = (torch.empty(B * T, dtype=torch.int32, device=dev) for _ in range(3))
+            n_live = torch.empty((), dtype=torch.int32, device=dev)
+        check(lib.b200sft_label_frontend(_ptr(input_ids), _ptr(labels), _ptr(attention_mask), _ptr(completion_mask),
+                                         _ptr(position_ids), B, T, ignore_index, _ptr(labels_out), _ptr(shifted),
+                                         _ptr(counts), _ptr(row_index), _ptr(labels_c), _ptr(pos), _ptr(n_live),
+                                         _stream_ptr(src)), "b200sft_label_frontend")
+        if B * T:
+            STATS.kernel_launches += 1
+    return LabelPlan(shifted, counts, labels_out, row_index, labels_c, pos, n_live)
+
+
+def gather_rows(x: torch.Tensor, plan: LabelPlan) -> torch.Tensor:
+    """``xc[j] = x[plan.row_index[j]]`` for the live rows of a :class:`LabelPlan` (zero rows up to the
+    next 128-row boundary): the gather half of :func:`compact_rows`."""
+    _require_cuda(x, plan.row_index, plan.n_live)
+    if x.dtype != torch.bfloat16 or x.dim() != 2 or not x.is_contiguous() or plan.row_index.shape != (x.shape[0],):
+        raise ValueError("x must be contiguous bf16 [N,H] with one plan entry per row")
+    N, H = x.shape
+    if N == 0:
+        return x
+    lib = _cabi.load()
+    with torch.cuda.device(x.device):
+        xc = torch.empty_like(x)
+        check(lib.b200sft_gather_rows(_ptr(x), _ptr(plan.row_index), _ptr(plan.n_live), N, H, _ptr(xc),
+                                      _stream_ptr(x)), "b200sft_gather_rows")
+        STATS.kernel_launches += 1
+    return xc
+
+
 def _check_flce_inputs(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> Tuple[int, int, int]:
     _require_cuda(x, w, labels)
     if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
@@ -354,10 +422,12 @@ def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols
 class _FusedLinearCrossEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_cols, skip_ignored,
-                with_stats):
+                with_stats, plan):
         pos = n_rows = None
         xk, lk = x, labels
-        if skip_ignored:  # run every GEMM on the live rows only
+        if skip_ignored and plan is not None and plan.row_index is not None:
+            xk, lk, pos, n_rows = gather_rows(x, plan), plan.labels_c, plan.pos, plan.n_live  # list already made
+        elif skip_ignored:  # run every GEMM on the live rows only
             xk, lk, _row_index, pos, n_rows = compact_rows(x, labels, ignore_index)
         loss, lse, n_valid, n_correct, entropy_sum = torch.ops.b200sft.flce_fwd(
             xk, w, lk, scale, denom, reduction_mean, ignore_index, flags, n_rows, with_stats)
@@ -375,13 +445,14 @@ class _FusedLinearCrossEntropy(torch.autograd.Function):
         dx, dw = torch.ops.b200sft.flce_bwd(xk, w, lk, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
                                             ctx.flags, ctx.chunk_cols, n_rows, need_dx, need_dw)
         dx = None if not need_dx else (scatter_rows(dx, pos) if pos is not None else dx)
-        return dx, (dw if need_dw else None), None, None, None, None, None, None, None, None, None
+        return dx, (dw if need_dw else None), None, None, None, None, None, None, None, None, None, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,
                                num_items_in_batch: Optional[torch.Tensor] = None, scale: float = 1.0,
                                ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0,
-                               skip_ignored_rows: bool = False, return_stats: bool = False):
+                               skip_ignored_rows: bool = False, return_stats: bool = False,
+                               plan: Optional[LabelPlan] = None):
     """Differentiable ``cross_entropy(hidden @ weight.T, shifted_labels)`` without the logits.
 
     ``num_items_in_batch`` None -> mean over local valid rows (``reduction="mean"``), else the
@@ -390,7 +461,8 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shift
     :func:`label_prep`.  ``skip_ignored_rows`` compacts away rows labelled ``ignore_index`` first
     (same result; less work when many rows are masked).  ``return_stats`` -> ``(loss, stats)`` with
     ``stats = {"n_valid", "n_correct", "entropy_sum"}`` device scalars (token accuracy and mean
-    entropy are n_correct / n_valid and entropy_sum / n_valid).
+    entropy are n_correct / n_valid and entropy_sum / n_valid).  ``plan``: the :class:`LabelPlan`
+    ``shifted_labels`` came from; its compaction list is then reused instead of being rebuilt.
     """
     denom = None
     if num_items_in_batch is not None:
@@ -399,7 +471,7 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shift
         denom = num_items_in_batch.to(device=hidden.device, dtype=torch.int64).reshape(())
     loss, n_valid, n_correct, entropy_sum = _FusedLinearCrossEntropy.apply(
         hidden, weight, shifted_labels, float(scale), denom, num_items_in_batch is None, ignore_index, flags,
-        chunk_cols, bool(skip_ignored_rows), bool(return_stats))
+        chunk_cols, bool(skip_ignored_rows), bool(return_stats), plan)
     if return_stats:
         return loss, {"n_valid": n_valid, "n_correct": n_correct, "entropy_sum": entropy_sum}
     return loss

@@ -28,6 +28,7 @@ import torch.distributed as dist
 import torch.nn as nn
 from torch.nn.parallel import DistributedDataParallel as DDP
 
+from . import ops
 from .loss import FusedCELossMixin
 
 MODEL_NAME = "HuggingFaceTB/SmolLM3-3B"  # training.py:54
@@ -187,15 +188,28 @@ class ByteChatTokenizer:
 
 
 def collate(samples: List[List[int]], pad_id: int, max_len: int, pad_to: Optional[int] = None,
-            masks: Optional[List[List[int]]] = None) -> Dict[str, torch.Tensor]:
+            masks: Optional[List[List[int]]] = None, device_labels: bool = False) -> Dict[str, torch.Tensor]:
     """[TRL collator semantics, SURVEY.md a3] truncate to ``max_len``, right-pad ``input_ids`` with
     the pad id, ``attention_mask`` with 0 and ``labels`` with -100.  Padding is the only mask the
-    reference produces for plain ``messages`` data."""
+    reference produces for plain ``messages`` data.  ``device_labels``: leave ``labels`` out and hand
+    over the raw masks (``completion_mask`` when ``masks`` is given); ``ops.label_frontend`` then
+    builds the same labels on the GPU."""
     samples = [s[:max_len] for s in samples]
     width = pad_to or max(len(s) for s in samples)
     B = len(samples)
     input_ids = torch.full((B, width), pad_id, dtype=torch.int64)
     attn = torch.zeros((B, width), dtype=torch.int64)
+    if device_labels:
+        comp = torch.zeros((B, width), dtype=torch.int64) if masks is not None else None
+        for i, s in enumerate(samples):
+            input_ids[i, : len(s)] = torch.tensor(s, dtype=torch.int64)
+            attn[i, : len(s)] = 1
+            if comp is not None:
+                comp[i, : len(s)] = torch.tensor(masks[i][: len(s)], dtype=torch.int64).ne(0)
+        out = {"input_ids": input_ids, "attention_mask": attn}
+        if comp is not None:
+            out["completion_mask"] = comp
+        return out
     labels = torch.full((B, width), -100, dtype=torch.int64)
     for i, s in enumerate(samples):
         t = torch.tensor(s, dtype=torch.int64)
@@ -209,31 +223,39 @@ def collate(samples: List[List[int]], pad_id: int, max_len: int, pad_to: Optiona
 
 
 def collate_flattened(samples: List[List[int]], max_len: int, masks: Optional[List[List[int]]] = None,
-                      separator_id: int = -100) -> Dict[str, Any]:
+                      separator_id: int = -100, device_labels: bool = False) -> Dict[str, Any]:
     """Padding-free batch, as ``transformers.DataCollatorWithFlattening(return_flash_attn_kwargs=True)``
     builds it (SP/transformers/data/data_collator.py:1364-1470): the samples are concatenated into one
     ``[1, total]`` row, ``position_ids`` restart at every sample, the first label of every sample is
     ``separator_id`` (:1426-1428) so no sample is scored against its predecessor, and the FlashAttention
     varlen arguments (``cu_seq_lens_*`` int32, ``max_length_*`` int) ride along.  ``masks`` (0/1 per
-    token) additionally turn non-assistant tokens into -100 (completion-only loss)."""
+    token) additionally turn non-assistant tokens into -100 (completion-only loss).  ``device_labels``:
+    no ``labels``; ``position_ids`` (and ``completion_mask``) are what ``ops.label_frontend`` makes them from."""
     samples = [s[:max_len] for s in samples]
     ids: List[int] = []
     labels: List[int] = []
+    comp: List[int] = []
     pos: List[int] = []
     cu = [0]
     for i, smp in enumerate(samples):
         lab = list(smp)
         if masks is not None:
             lab = [t if m else -100 for t, m in zip(smp, masks[i][:max_len])]
+            comp += [1 if m else 0 for m in masks[i][: len(smp)]]
         ids += smp
         labels += [separator_id] + lab[1:]
         pos += list(range(len(smp)))
         cu.append(cu[-1] + len(smp))
     longest = max(len(smp) for smp in samples)
-    return {"input_ids": torch.tensor([ids], dtype=torch.int64), "labels": torch.tensor([labels], dtype=torch.int64),
-            "position_ids": torch.tensor([pos], dtype=torch.int64),
-            "cu_seq_lens_q": torch.tensor(cu, dtype=torch.int32), "cu_seq_lens_k": torch.tensor(cu, dtype=torch.int32),
-            "max_length_q": longest, "max_length_k": longest}
+    out = {"input_ids": torch.tensor([ids], dtype=torch.int64), "labels": torch.tensor([labels], dtype=torch.int64),
+           "position_ids": torch.tensor([pos], dtype=torch.int64),
+           "cu_seq_lens_q": torch.tensor(cu, dtype=torch.int32), "cu_seq_lens_k": torch.tensor(cu, dtype=torch.int32),
+           "max_length_q": longest, "max_length_k": longest}
+    if device_labels:
+        del out["labels"]
+        if masks is not None:
+            out["completion_mask"] = torch.tensor([comp], dtype=torch.int64)
+    return out
 
 
 class ShardedBatches:
@@ -241,10 +263,10 @@ class ShardedBatches:
     ragged tail (``dataloader_drop_last=True``, training.py:281)."""
 
     def __init__(self, tokens: List[List[int]], batch_size: int, rank: int, world: int, pad_id: int, max_len: int, seed: int,
-                 masks: Optional[List[List[int]]] = None, padding_free: bool = False):
+                 masks: Optional[List[List[int]]] = None, padding_free: bool = False, device_labels: bool = False):
         self.tokens, self.bs, self.rank, self.world = tokens, batch_size, rank, world
         self.pad_id, self.max_len, self.seed = pad_id, max_len, seed
-        self.masks, self.padding_free = masks, padding_free
+        self.masks, self.padding_free, self.device_labels = masks, padding_free, device_labels
 
     def __len__(self) -> int:
         return len(self.tokens) // (self.bs * self.world)
@@ -258,9 +280,9 @@ class ShardedBatches:
             toks = [self.tokens[i] for i in chunk]
             msk = [self.masks[i] for i in chunk] if self.masks is not None else None
             if self.padding_free:
-                yield collate_flattened(toks, self.max_len, msk)
+                yield collate_flattened(toks, self.max_len, msk, device_labels=self.device_labels)
             else:
-                yield collate(toks, self.pad_id, self.max_len, masks=msk)
+                yield collate(toks, self.pad_id, self.max_len, masks=msk, device_labels=self.device_labels)
 
 
 # --------------------------------------------------------------------------------------------
@@ -359,16 +381,34 @@ class MiniSFTTrainer(FusedCELossMixin):
                 break
         if not batches:
             return batches, None
-        count = sum(b["labels"].ne(-100).sum() for b in batches).to(self.device)
+        if any("labels" not in b for b in batches):  # labels are built on the device; the count comes with them
+            batches = [self._on_device(b) for b in batches]
+            count = sum(b["b200sft_plan"].counts[0] if "b200sft_plan" in b else b["labels"].ne(-100).sum()
+                        for b in batches)
+        else:
+            count = sum(b["labels"].ne(-100).sum() for b in batches).to(self.device)
         if self.args.average_tokens_across_devices and self.world > 1:
             dist.all_reduce(count, op=dist.ReduceOp.SUM)
         return batches, count
+
+    def _on_device(self, inputs: Dict[str, Any]) -> Dict[str, Any]:
+        """H2D; when the collator left ``labels`` out (``device_labels``) build them here with the label
+        front-end -- one launch gives the labels, the window's count and the plan the fused loss reuses."""
+        inputs = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in inputs.items()}
+        if "labels" not in inputs:
+            plan = ops.label_frontend(inputs["input_ids"], None, inputs.get("attention_mask"),
+                                      inputs.pop("completion_mask", None), inputs.get("position_ids"),
+                                      compact=bool(getattr(self, "b200sft_skip_ignored_rows", True)), return_labels=True)
+            inputs["labels"] = plan.labels
+            if self.loss_impl is None:
+                inputs["b200sft_plan"] = plan
+        return inputs
 
     def training_step(self, inputs: Dict[str, torch.Tensor], num_items_in_batch: Optional[torch.Tensor]) -> torch.Tensor:
         """trainer.py:1867-1936 for this configuration: H2D, compute_loss, backward.  No division
         by the accumulation steps: the loss is already normalised by the window's token count."""
         self.model_wrapped.train()
-        inputs = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in inputs.items()}
+        inputs = self._on_device(inputs)
         if self.loss_impl is not None:
             loss = self.loss_impl(self.model_wrapped, inputs, num_items_in_batch)
             if num_items_in_batch is not None and self.args.average_tokens_across_devices:
@@ -397,7 +437,7 @@ class MiniSFTTrainer(FusedCELossMixin):
         total = torch.zeros((), device=self.device)
         n = 0
         for inputs in self.eval_batches.epoch(0):
-            inputs = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in inputs.items()}
+            inputs = self._on_device(inputs)
             if self.loss_impl is not None:
                 total += self.loss_impl(self.model, inputs, None).float()
             else:
@@ -501,7 +541,8 @@ def build_trainer(model: nn.Module, settings: SFTSettings, train_rows, val_rows,
         else:
             toks, masks = [tokenizer.apply_chat_template(m) for m in msgs], None
         return ShardedBatches(toks, bs, rank, world, tokenizer.pad_token_id, settings.max_seq_length, settings.seed,
-                              masks=masks, padding_free=settings.packing)
+                              masks=masks, padding_free=settings.packing,
+                              device_labels=os.getenv("DEVICE_LABELS", "0") == "1")  # labels built by ops.label_frontend
 
     return MiniSFTTrainer(model, settings, mk(train_rows, settings.per_device_train_batch_size),
                           mk(val_rows, settings.per_device_eval_batch_size), callbacks=callbacks, **mini_kwargs)
@@ -568,6 +609,7 @@ def main() -> None:  # mirrors training.py:49-349
                 attn = "flash_attention_2"
             except Exception:
                 attn = None
+        torch.manual_seed(settings.seed)  # random init is the only seeded draw before Trainer's own set_seed(args.seed)
         model = make_model(os.getenv("MODEL_CONFIG", "3b"), device, attn)
     if tokenizer is None:
         tokenizer = ByteChatTokenizer(model.config.vocab_size)

@@ -84,3 +84,25 @@ def test_driver_two_gpus_ddp(cuda_device, tmp_path, comm):
                          timeout=400)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
     _check(tmp_path, 2)
+
+
+@pytest.mark.parametrize("extra", [dict(COMPLETION_ONLY="1"),
+                                   dict(PACKING="1", COMPLETION_ONLY="1", ATTN_IMPL="flash_attention_2")],
+                         ids=["padded", "packed"])
+def test_driver_device_labels_same_run(cuda_device, tmp_path, extra):
+    """DEVICE_LABELS=1: the collator ships raw masks and b200sft_label_frontend builds labels, counts and the
+    compaction list on the GPU.  Same data, same seed -> the same losses as with host-made labels."""
+    _write_parquet(tmp_path / "qa.parquet")
+    histories = []
+    for flag in ("0", "1"):
+        res = subprocess.run([sys.executable, "-m", "llm_fine_tune_distributed_b200.training"], cwd=ROOT,
+                             env=_env(tmp_path, WORLD_SIZE="1", RANK="0", LOCAL_RANK="0", DEVICE_LABELS=flag, **extra),
+                             capture_output=True, text=True, timeout=300)
+        assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+        _check(tmp_path, 1)
+        histories.append(json.load(open(tmp_path / "out" / "training_history.json")))
+    host, dev = ([h["loss"] for h in hist if "loss" in h] for hist in histories)
+    assert host[0] == dev[0]  # first window: identical labels through identical kernels
+    assert dev == pytest.approx(host, rel=1e-3)
+    ev = [[h["eval_loss"] for h in hist if "eval_loss" in h] for hist in histories]
+    assert ev[1] == pytest.approx(ev[0], rel=1e-3)

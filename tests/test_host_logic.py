@@ -139,6 +139,53 @@ def test_completion_only_masks():
     assert int((flat["labels"] != -100).sum()) == 2 * n_assistant and flat["position_ids"][0, len(ids)] == 0
 
 
+def test_device_label_collators_carry_what_the_frontend_needs():
+    """device_labels=True: no labels leave the host; masks + the front-end's rule reproduce exactly the labels
+    the host collators write (padded and padding-free, with and without completion masks)."""
+    from llm_fine_tune_distributed_b200.training import collate, collate_flattened
+
+    rng = np.random.default_rng(0)
+    samples = [rng.integers(3, 900, size=n).tolist() for n in (7, 1, 12, 5)]
+    masks = [(rng.random(len(s)) > 0.4).astype(int).tolist() for s in samples]
+    for m in (None, masks):
+        host, dev = collate(samples, 0, 10, masks=m), collate(samples, 0, 10, masks=m, device_labels=True)
+        assert "labels" not in dev and ("completion_mask" in dev) == (m is not None)
+        got = oracle.collator_labels_numpy(dev["input_ids"].numpy(), None, dev["attention_mask"].numpy(),
+                                           dev["completion_mask"].numpy() if m else None)
+        np.testing.assert_array_equal(got, host["labels"].numpy())
+        host, dev = collate_flattened(samples, 10, m), collate_flattened(samples, 10, m, device_labels=True)
+        assert "labels" not in dev and set(host) - set(dev) == {"labels"}
+        got = oracle.collator_labels_numpy(dev["input_ids"].numpy(), None, None,
+                                           dev["completion_mask"].numpy() if m else None, dev["position_ids"].numpy())
+        np.testing.assert_array_equal(got, host["labels"].numpy())
+
+
+def test_compute_loss_seam_takes_a_label_plan(tiny, monkeypatch):
+    """A batch that arrives with ``b200sft_plan`` (labels built by the front-end ahead of the forward) gives the
+    loss of the plain call; the plan never reaches the model's forward."""
+    from llm_fine_tune_distributed_b200 import FusedCELossMixin, install_fused_head, ops
+
+    _cpu_standins.install(monkeypatch)
+    install_fused_head(tiny)
+    d = np.load(os.path.join(G, "smollm3_tiny_step.npz"))
+
+    class Seam(FusedCELossMixin):
+        num_processes = 1
+        model_accepts_loss_kwargs = True
+        args = None
+
+    ids, labels = torch.from_numpy(d["input_ids_0"]), torch.from_numpy(d["labels_0"])
+    plan = ops.label_frontend(labels=labels, return_labels=True)
+    seam = Seam()
+    n = torch.tensor(int(d["num_items"]))
+    a = seam.compute_loss(tiny, {"input_ids": ids, "labels": labels}, num_items_in_batch=n)
+    b = seam.compute_loss(tiny, {"input_ids": ids, "labels": plan.labels, "b200sft_plan": plan}, num_items_in_batch=n)
+    assert float(a) == float(b) and tiny.lm_head.plan is None
+    wrong = ops.label_frontend(labels=labels[:, :-1].contiguous())
+    with pytest.raises(ValueError):
+        seam.compute_loss(tiny, {"input_ids": ids, "labels": labels, "b200sft_plan": wrong}, num_items_in_batch=n)
+
+
 def test_patched_model_saves_and_reloads_as_stock(tiny, tmp_path):
     """The head swap must not leak into checkpoints: save_pretrained on the patched model, then a
     stock from_pretrained, gives the same logits (training.py:309-312 saves the best model this way)."""

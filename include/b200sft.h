@@ -91,7 +91,9 @@ int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, cons
  * max / sum-exp per row.
  *   x        [N,H] bf16   final hidden states (already shifted-aligned with `labels`)
  *   w        [V,H] bf16   lm_head.weight (tied to embed_tokens.weight)
- *   labels   [N]   int32  shifted labels; ignore_index rows contribute nothing
+ *   labels   [N]   int32  shifted labels; ignore_index rows contribute nothing.  Any other label
+ *            outside [0,V) makes the loss NaN (the reference trips nll_loss's device assert there;
+ *            a kernel cannot raise, and the host never reads the labels).
  *   denom    int64 scalar (device) used when denom_mode == B200SFT_DENOM_DEVICE, else may be NULL
  *   n_rows_dev  int32 scalar (device) or NULL: number of live rows (<= N) when x/labels are the
  *            compacted tensors from b200sft_compact_rows; N is then the capacity.  NULL = all N rows.

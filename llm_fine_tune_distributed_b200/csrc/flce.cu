@@ -314,7 +314,7 @@ constexpr int MERGE_LANES = 8;   // threads per row, each folding every 8th voca
 __global__ void __launch_bounds__(MERGE_ROWS* MERGE_LANES)
     flce_merge_rows_kernel(const float2* __restrict__ partials, const float* __restrict__ partials_ez,
                            const float* __restrict__ tgt_logit, const int32_t* __restrict__ labels, int rows_cap,
-                           const int* __restrict__ n_rows_dev, int tiles_n, int ignore_index, float* __restrict__ lse,
+                           const int* __restrict__ n_rows_dev, int tiles_n, int V, int ignore_index, float* __restrict__ lse,
                            float* __restrict__ row_loss, float* __restrict__ row_entropy,
                            unsigned char* __restrict__ row_correct) {
   const int M = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
@@ -353,7 +353,10 @@ __global__ void __launch_bounds__(MERGE_ROWS* MERGE_LANES)
   const int lbl = labels[row];
   const bool valid = lbl != ignore_index;
   const float tgt = tgt_logit[row];
-  row_loss[row] = valid ? (l - tgt) : 0.f;
+  // A label outside [0,V) that is not ignore_index trips a device assert in the reference
+  // (nll_loss); nothing here can raise, so the row -- and with it the loss -- turns NaN instead.
+  const bool in_range = static_cast<unsigned int>(lbl) < static_cast<unsigned int>(V);
+  row_loss[row] = valid ? (in_range ? (l - tgt) : __int_as_float(0x7fc00000)) : 0.f;
   if (partials_ez) {
     row_entropy[row] = valid ? (l - ez / sum) : 0.f;
     row_correct[row] = (valid && tgt >= m) ? 1 : 0;  // the target logit is the row maximum
@@ -761,7 +764,7 @@ int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, in
   const FwdScratch f = carve_fwd(workspace, N, V, stats);
   const int tiles_n = (V + BLOCK_N - 1) / BLOCK_N;
 
-  // Rows whose label is ignored (or, defensively, outside [0,V)) never get a target logit written.
+  // Rows whose label is ignored (or outside [0,V): those make the loss NaN) never get a target logit written.
   B200_CUDA_CHECK(cudaMemsetAsync(f.tgt, 0, static_cast<size_t>(N) * sizeof(float), stream));
 
   if (stats) {
@@ -776,7 +779,7 @@ int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, in
   if (rc != 0) return rc;
 
   flce_merge_rows_kernel<<<(N + MERGE_ROWS - 1) / MERGE_ROWS, MERGE_ROWS * MERGE_LANES, 0, stream>>>(f.partials, f.partials_ez, f.tgt, labels, N, n_rows_dev,
-                                                               tiles_n, ignore_index, lse, f.row_loss, f.row_entropy,
+                                                               tiles_n, V, ignore_index, lse, f.row_loss, f.row_entropy,
                                                                f.row_correct);
   B200_CUDA_CHECK(cudaGetLastError());
   flce_reduce_loss_kernel<<<1, 1024, 0, stream>>>(f.row_loss, f.row_entropy, f.row_correct, labels, N, n_rows_dev,

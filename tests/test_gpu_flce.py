@@ -351,3 +351,22 @@ def test_flce_empty_batch_matches_torch(cuda_device, skip):
     assert x.grad.shape == (0, H) and torch.count_nonzero(w.grad) == 0
     mean = ops.fused_linear_cross_entropy(x.detach(), w.detach(), labels, None, skip_ignored_rows=skip)
     assert torch.isnan(mean) and torch.isnan(oracle.lm_head_ce(x.detach(), w.detach(), labels.long(), None))
+
+
+@pytest.mark.parametrize("bad", [512, 100000, -7])
+def test_flce_out_of_range_label_poisons_the_loss(cuda_device, bad):
+    """torch refuses a target outside [0,V) (IndexError on CPU, device assert on CUDA).  The fused
+    path cannot raise from a kernel; it must not return a finite, wrong loss either."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    N, H, V = 256, 64, 512
+    x = torch.randn(N, H, device=cuda_device).to(torch.bfloat16)
+    w = torch.randn(V, H, device=cuda_device).to(torch.bfloat16)
+    labels = torch.randint(0, V, (N,), device=cuda_device, dtype=torch.int32)
+    good = ops.fused_linear_cross_entropy(x, w, labels, None)
+    assert torch.isfinite(good)
+    labels[17] = bad
+    with pytest.raises((IndexError, RuntimeError)):
+        oracle.lm_head_ce(x.cpu(), w.cpu(), labels.cpu().long(), None)
+    for skip in (False, True):
+        assert torch.isnan(ops.fused_linear_cross_entropy(x, w, labels, None, skip_ignored_rows=skip))

@@ -74,7 +74,7 @@ def _rows():
     return [{"full-question": f"For topic {i}, how do I do thing {i}?", "answer": "Carefully. " * (i % 7 + 1)} for i in range(64)]
 
 
-def _train_worker(rank, world, port, ret):
+def _train_worker(rank, world, port, ret, device_labels=False):
     _init(rank, world, port)
     import _cpu_standins
 
@@ -92,7 +92,8 @@ def _train_worker(rank, world, port, ret):
     tokens = [tok.apply_chat_template(format_prompt(r)["messages"]) for r in _rows()]
     args = SFTSettings(per_device_train_batch_size=2, gradient_accumulation_steps=2, max_steps=2, max_seq_length=48,
                        gradient_checkpointing=False, learning_rate=1e-3, logging_steps=1)
-    batches = ShardedBatches(tokens, 2, rank, world, tok.pad_token_id, args.max_seq_length, seed=42)
+    batches = ShardedBatches(tokens, 2, rank, world, tok.pad_token_id, args.max_seq_length, seed=42,
+                             device_labels=device_labels)
     state = B200HookState(None, scale_fn=lambda buf, s: buf.mul_(s))
     logs = []
 
@@ -126,3 +127,19 @@ def test_config1_tiny_smollm3_sft_gloo_world2():
     assert r0["logs"][0]["loss"] == r1["logs"][0]["loss"]
     assert 8.0 < r0["logs"][0]["loss"] < 16.0
     assert r0["tokens"] == r1["tokens"] > 0
+
+
+@pytest.mark.timeout(600)
+def test_device_labels_window_count_gloo_world2():
+    """Labels built by the label front-end (stand-in on CPU) instead of the collator: the window's
+    num_items_in_batch now comes from the front-end's count and is still summed over ranks, so the
+    logged losses equal the host-label run's and the replicas stay in step."""
+    runs = []
+    for port, flag in ((29641, False), (29651, True)):
+        ret = mp.Manager().dict()
+        mp.spawn(_train_worker, args=(2, port, ret, flag), nprocs=2, join=True)
+        assert ret[0]["replicas_equal"] and ret[1]["replicas_equal"]
+        assert ret[0]["logs"][0]["loss"] == ret[1]["logs"][0]["loss"]
+        runs.append(ret[0])
+    assert [l["loss"] for l in runs[0]["logs"]] == [l["loss"] for l in runs[1]["logs"]]
+    assert runs[0]["tokens"] == runs[1]["tokens"]

@@ -3,11 +3,14 @@
 // contiguous 16 KiB run (measured faster on B200 than a persistent grid-stride sweep, whose
 // per-thread accesses land megabytes apart); vector accesses are 8/16 bytes, 4 in flight per thread.
 #include <cuda_bf16.h>
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/b200sft.h"
 #include "capi_common.h"
+
+namespace cg = cooperative_groups;
 
 namespace b200 {
 
@@ -88,9 +91,10 @@ __global__ void label_prep_kernel(const int64_t* __restrict__ labels, int B, int
 //   attention_mask[i] == 0 (padding), completion_mask[i] == 0 (prompt tokens under
 //   completion-only loss) or position_ids[i] == 0 (first token of a packed sequence -- the
 //   separator DataCollatorWithFlattening writes, SP/transformers/data/data_collator.py:1426-1428).
-// One 1024-thread block: each warp owns one contiguous run and walks it 32 tokens at a time
+// 1024-thread blocks: each warp owns one contiguous run and walks it 32 tokens at a time
 // (coalesced), so the stable compaction is a ballot + popc per step and one 32-entry scan over
 // the warp totals.  Nothing needs zeroing beforehand and nothing is accumulated with atomics.
+// One block up to 16 Ki tokens; beyond that one 8-CTA cluster (see the kernel).
 struct LabelSources {
   const int64_t* src;
   const int64_t* attention_mask;
@@ -107,17 +111,28 @@ struct LabelSources {
 };
 
 constexpr int FRONTEND_THREADS = 1024;
+constexpr int FRONTEND_CLUSTER = 8;               // CTAs of the cluster variant (portable maximum)
+constexpr size_t FRONTEND_CLUSTER_MIN = 16384;    // tokens from which one block's latency shows (measured)
 
+// CLUSTER == 1: one block.  CLUSTER == 8: one thread-block cluster; every CTA scans its own 32 warp
+// totals, the per-CTA totals are exchanged through distributed shared memory (8 remote reads per
+// CTA), so the cross-CTA prefix needs neither a second launch nor global-memory flags.
+template <int CLUSTER>
 __global__ void __launch_bounds__(FRONTEND_THREADS)
 label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ labels_out, int32_t* __restrict__ shifted,
                       int64_t* __restrict__ counts, int32_t* __restrict__ row_index, int32_t* __restrict__ labels_c,
                       int32_t* __restrict__ pos, int32_t* __restrict__ n_live) {
-  __shared__ unsigned int s_live[32], s_unshifted[32], s_base[33];
+  __shared__ unsigned int s_live[32], s_unshifted[32], s_base[32];
+  __shared__ unsigned int s_cta_total[2];  // this CTA's live / unshifted totals (read by the other CTAs)
+  __shared__ unsigned int s_grand[3];      // live rows in lower-ranked CTAs, all live rows, all unshifted
+  unsigned int cta_rank = 0;
+  if constexpr (CLUSTER > 1) cta_rank = cg::this_cluster().block_rank();
   const size_t total = static_cast<size_t>(B) * T;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned int lt_mask = (1u << lane) - 1u;
-  const size_t per = ((total + 31) / 32 + 31) / 32 * 32;  // tokens per warp, a multiple of 32
-  const size_t lo = min(static_cast<size_t>(warp) * per, total), hi = min(lo + per, total);
+  const size_t n_warps = static_cast<size_t>(CLUSTER) * 32;
+  const size_t per = ((total + n_warps - 1) / n_warps + 31) / 32 * 32;  // tokens per warp, a multiple of 32
+  const size_t lo = min((static_cast<size_t>(cta_rank) * 32 + warp) * per, total), hi = min(lo + per, total);
   const int32_t ignore32 = static_cast<int32_t>(in.ignore_index);
 
   // pass 1: labels, shifted labels, per-warp counts
@@ -142,7 +157,7 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
     s_unshifted[warp] = unshifted;
   }
   __syncthreads();
-  if (warp == 0) {  // exclusive scan of the 32 warp totals
+  if (warp == 0) {  // exclusive scan of this CTA's 32 warp totals
     unsigned int v = s_live[lane], u = s_unshifted[lane];
     unsigned int incl = v;
     for (int off = 1; off < 32; off <<= 1) {
@@ -151,19 +166,51 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
       u += __shfl_xor_sync(0xffffffffu, u, off);
     }
     s_base[lane] = incl - v;
-    if (lane == 31) s_base[32] = incl;
-    if (lane == 0) counts[0] = static_cast<int64_t>(u);
+    if (lane == 31) s_cta_total[0] = incl;
+    if (lane == 0) s_cta_total[1] = u;
   }
-  __syncthreads();
-  const unsigned int n_total = s_base[32];
-  if (threadIdx.x == 0) {
+  if constexpr (CLUSTER > 1) {
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();  // every CTA's totals are in its shared memory
+    if (warp == 0) {
+      unsigned int l = 0, u = 0;
+      if (lane < CLUSTER) {
+        const unsigned int* remote = cluster.map_shared_rank(s_cta_total, lane);
+        l = remote[0];
+        u = remote[1];
+      }
+      unsigned int below = lane < static_cast<int>(cta_rank) ? l : 0u;
+      for (int off = 16; off > 0; off >>= 1) {
+        l += __shfl_xor_sync(0xffffffffu, l, off);
+        u += __shfl_xor_sync(0xffffffffu, u, off);
+        below += __shfl_xor_sync(0xffffffffu, below, off);
+      }
+      if (lane == 0) {
+        s_grand[0] = below;
+        s_grand[1] = l;
+        s_grand[2] = u;
+      }
+    }
+    cluster.sync();  // s_grand is visible; no CTA leaves while a neighbour may still read its totals
+  } else {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      s_grand[0] = 0;
+      s_grand[1] = s_cta_total[0];
+      s_grand[2] = s_cta_total[1];
+    }
+    __syncthreads();
+  }
+  const unsigned int n_total = s_grand[1];
+  if (cta_rank == 0 && threadIdx.x == 0) {
+    counts[0] = static_cast<int64_t>(s_grand[2]);
     counts[1] = static_cast<int64_t>(n_total);
     if (n_live != nullptr) *n_live = static_cast<int32_t>(n_total);
   }
   if (row_index == nullptr) return;
 
   // pass 2: stable compaction (each thread re-reads the shifted labels it wrote itself)
-  unsigned int at = s_base[warp];
+  unsigned int at = s_grand[0] + s_base[warp];
   for (size_t base = lo; base < hi; base += 32) {
     const size_t i = base + lane;
     int32_t l = ignore32;
@@ -180,7 +227,9 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
     }
     at += __popc(ballot);
   }
-  for (size_t j = n_total + threadIdx.x; j < total; j += blockDim.x) labels_c[j] = ignore32;  // dead tail
+  for (size_t j = n_total + cta_rank * FRONTEND_THREADS + threadIdx.x; j < total;
+       j += static_cast<size_t>(CLUSTER) * FRONTEND_THREADS)
+    labels_c[j] = ignore32;  // dead tail
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -370,9 +419,25 @@ int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, cons
   if (compact && !(row_index && labels_c && pos && n_live))
     return fail(B200SFT_ERR_INVALID, "compaction outputs must be all set or all null");
   LabelSources in{src, attention_mask, completion_mask, position_ids, ignore_index};
-  label_frontend_kernel<<<1, FRONTEND_THREADS, 0, stream>>>(in, B, T, labels_out, shifted, counts, row_index, labels_c,
-                                                             pos, n_live);
-  B200_CUDA_CHECK(cudaGetLastError());
+  if (total < FRONTEND_CLUSTER_MIN) {
+    label_frontend_kernel<1><<<1, FRONTEND_THREADS, 0, stream>>>(in, B, T, labels_out, shifted, counts, row_index,
+                                                                  labels_c, pos, n_live);
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200SFT_OK;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(FRONTEND_CLUSTER);
+  cfg.blockDim = dim3(FRONTEND_THREADS);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = FRONTEND_CLUSTER;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, label_frontend_kernel<FRONTEND_CLUSTER>, in, B, T, labels_out, shifted, counts,
+                                     row_index, labels_c, pos, n_live));
   return B200SFT_OK;
 }
 

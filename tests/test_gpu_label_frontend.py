@@ -50,7 +50,9 @@ def _check(plan, want, compact=True):
     np.testing.assert_array_equal(plan.pos.cpu().numpy(), want["pos"])
 
 
-@pytest.mark.parametrize("B,T", [(1, 1), (1, 31), (3, 32), (2, 1023), (8, 1024), (5, 777), (1, 65536), (64, 1)])
+# up to 16383 tokens: one block; from 16384: one 8-CTA cluster exchanging totals through distributed shared memory
+@pytest.mark.parametrize("B,T", [(1, 1), (1, 31), (3, 32), (2, 1023), (8, 1024), (5, 777), (1, 65536), (64, 1),
+                                 (1, 16383), (4, 4096), (3, 5462), (5, 7001), (8, 8192), (16385, 1)])
 @pytest.mark.parametrize("masks", [(), ("labels",), ("att",), ("labels", "comp"), ("pos",), ("labels", "att", "comp", "pos")])
 def test_label_frontend_matches_oracle(cuda_device, B, T, masks):
     from llm_fine_tune_distributed_b200 import ops

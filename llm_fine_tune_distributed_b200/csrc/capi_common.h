@@ -32,4 +32,8 @@ inline int fail(int code, const char* msg) {
                           __LINE__);                                                                       \
   } while (0)
 
+// elementwise.cu: stable compaction list of shifted int32 labels (the label front-end kernel, shift skipped)
+int launch_compact_labels(const int* labels, int N, int ignore_index, int* row_index, int* labels_c, int* pos,
+                          int* n_live, cudaStream_t stream);
+
 }  // namespace b200

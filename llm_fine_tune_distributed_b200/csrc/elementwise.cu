@@ -96,6 +96,7 @@ __global__ void label_prep_kernel(const int64_t* __restrict__ labels, int B, int
 // the warp totals.  Nothing needs zeroing beforehand and nothing is accumulated with atomics.
 // One block up to 16 Ki tokens; beyond that one 8-CTA cluster (see the kernel).
 struct LabelSources {
+  const int32_t* pre_shifted;  // non-null: labels are shifted int32 already; only the compaction runs
   const int64_t* src;
   const int64_t* attention_mask;
   const int64_t* completion_mask;
@@ -141,13 +142,17 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
     const size_t i = base + lane;
     bool is_live = false, is_unshifted = false;
     if (i < hi) {
-      const int64_t cur = in.at(i);
-      const int t = static_cast<int>(i % T);
-      const int64_t nxt = (t + 1 < T) ? in.at(i + 1) : in.ignore_index;
-      if (labels_out != nullptr) labels_out[i] = cur;
-      shifted[i] = static_cast<int32_t>(nxt);
-      is_unshifted = cur != in.ignore_index;
-      is_live = nxt != in.ignore_index;
+      if (in.pre_shifted != nullptr) {
+        is_live = in.pre_shifted[i] != ignore32;
+      } else {
+        const int64_t cur = in.at(i);
+        const int t = static_cast<int>(i % T);
+        const int64_t nxt = (t + 1 < T) ? in.at(i + 1) : in.ignore_index;
+        if (labels_out != nullptr) labels_out[i] = cur;
+        shifted[i] = static_cast<int32_t>(nxt);
+        is_unshifted = cur != in.ignore_index;
+        is_live = nxt != in.ignore_index;
+      }
     }
     live += __popc(__ballot_sync(0xffffffffu, is_live));
     unshifted += __popc(__ballot_sync(0xffffffffu, is_unshifted));
@@ -203,18 +208,21 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
   }
   const unsigned int n_total = s_grand[1];
   if (cta_rank == 0 && threadIdx.x == 0) {
-    counts[0] = static_cast<int64_t>(s_grand[2]);
-    counts[1] = static_cast<int64_t>(n_total);
+    if (counts != nullptr) {
+      counts[0] = static_cast<int64_t>(s_grand[2]);
+      counts[1] = static_cast<int64_t>(n_total);
+    }
     if (n_live != nullptr) *n_live = static_cast<int32_t>(n_total);
   }
   if (row_index == nullptr) return;
 
   // pass 2: stable compaction (each thread re-reads the shifted labels it wrote itself)
+  const int32_t* __restrict__ from = in.pre_shifted != nullptr ? in.pre_shifted : shifted;
   unsigned int at = s_grand[0] + s_base[warp];
   for (size_t base = lo; base < hi; base += 32) {
     const size_t i = base + lane;
     int32_t l = ignore32;
-    if (i < hi) l = shifted[i];
+    if (i < hi) l = from[i];
     const bool is_live = (i < hi) && l != ignore32;
     const unsigned int ballot = __ballot_sync(0xffffffffu, is_live);
     if (is_live) {
@@ -378,6 +386,44 @@ inline unsigned int stream_grid(size_t nvec) {
 
 using namespace b200;
 
+namespace b200 {
+
+// One block below FRONTEND_CLUSTER_MIN tokens, one 8-CTA cluster from there.
+static int launch_label_frontend(const LabelSources& in, int B, int T, int64_t* labels_out, int32_t* shifted,
+                                 int64_t* counts, int32_t* row_index, int32_t* labels_c, int32_t* pos, int32_t* n_live,
+                                 cudaStream_t stream) {
+  const size_t total = static_cast<size_t>(B) * T;
+  if (total < FRONTEND_CLUSTER_MIN) {
+    label_frontend_kernel<1><<<1, FRONTEND_THREADS, 0, stream>>>(in, B, T, labels_out, shifted, counts, row_index,
+                                                                  labels_c, pos, n_live);
+    B200_CUDA_CHECK(cudaGetLastError());
+    return B200SFT_OK;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(FRONTEND_CLUSTER);
+  cfg.blockDim = dim3(FRONTEND_THREADS);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = FRONTEND_CLUSTER;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, label_frontend_kernel<FRONTEND_CLUSTER>, in, B, T, labels_out, shifted, counts,
+                                     row_index, labels_c, pos, n_live));
+  return B200SFT_OK;
+}
+
+// Compaction list of already-shifted int32 labels (b200sft_compact_rows): the same kernel, shift skipped.
+int launch_compact_labels(const int32_t* labels, int N, int ignore_index, int32_t* row_index, int32_t* labels_c,
+                          int32_t* pos, int32_t* n_live, cudaStream_t stream) {
+  LabelSources in{labels, nullptr, nullptr, nullptr, nullptr, static_cast<int64_t>(ignore_index)};
+  return launch_label_frontend(in, 1, N, nullptr, nullptr, nullptr, row_index, labels_c, pos, n_live, stream);
+}
+
+}  // namespace b200
+
 extern "C" {
 
 const char* b200sft_last_error(void) { return last_error_buf(); }
@@ -418,27 +464,8 @@ int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, cons
   const bool compact = row_index || labels_c || pos || n_live;
   if (compact && !(row_index && labels_c && pos && n_live))
     return fail(B200SFT_ERR_INVALID, "compaction outputs must be all set or all null");
-  LabelSources in{src, attention_mask, completion_mask, position_ids, ignore_index};
-  if (total < FRONTEND_CLUSTER_MIN) {
-    label_frontend_kernel<1><<<1, FRONTEND_THREADS, 0, stream>>>(in, B, T, labels_out, shifted, counts, row_index,
-                                                                  labels_c, pos, n_live);
-    B200_CUDA_CHECK(cudaGetLastError());
-    return B200SFT_OK;
-  }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(FRONTEND_CLUSTER);
-  cfg.blockDim = dim3(FRONTEND_THREADS);
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = FRONTEND_CLUSTER;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, label_frontend_kernel<FRONTEND_CLUSTER>, in, B, T, labels_out, shifted, counts,
-                                     row_index, labels_c, pos, n_live));
-  return B200SFT_OK;
+  LabelSources in{nullptr, src, attention_mask, completion_mask, position_ids, ignore_index};
+  return launch_label_frontend(in, B, T, labels_out, shifted, counts, row_index, labels_c, pos, n_live, stream);
 }
 
 int b200sft_scale_bf16_inplace(void* buf, size_t n, float scale, void* stream_) {

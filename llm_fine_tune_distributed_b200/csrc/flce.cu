@@ -417,41 +417,8 @@ __global__ void flce_reduce_loss_kernel(const float* __restrict__ row_loss, cons
 // count stays on the device (GemmShape::dyn_rows); nothing here synchronises the host.
 // =============================================================================================
 
-// One block.  Stable compaction of the non-ignored rows:
-//   row_index[j] = original row of compact row j (j < n_live)      labels_c[j] = its label
-//   pos[r]       = compact position of original row r, or -1        *n_live    = live count
-__global__ void compact_labels_kernel(const int32_t* __restrict__ labels, int N, int ignore_index,
-                                      int32_t* __restrict__ row_index, int32_t* __restrict__ labels_c,
-                                      int32_t* __restrict__ pos, int* __restrict__ n_live) {
-  __shared__ int s_off[1024];
-  const int per = (N + blockDim.x - 1) / blockDim.x;
-  const int lo = min(static_cast<int>(threadIdx.x) * per, N), hi = min(lo + per, N);
-  int cnt = 0;
-  for (int i = lo; i < hi; ++i) cnt += (labels[i] != ignore_index) ? 1 : 0;
-  s_off[threadIdx.x] = cnt;
-  __syncthreads();
-  for (int off = 1; off < static_cast<int>(blockDim.x); off <<= 1) {  // inclusive Hillis-Steele scan
-    int v = (static_cast<int>(threadIdx.x) >= off) ? s_off[threadIdx.x - off] : 0;
-    __syncthreads();
-    s_off[threadIdx.x] += v;
-    __syncthreads();
-  }
-  int at = s_off[threadIdx.x] - cnt;
-  for (int i = lo; i < hi; ++i) {
-    const int l = labels[i];
-    if (l != ignore_index) {
-      row_index[at] = i;
-      labels_c[at] = l;
-      pos[i] = at;
-      ++at;
-    } else {
-      pos[i] = -1;
-    }
-  }
-  const int total = s_off[blockDim.x - 1];
-  for (int j = total + static_cast<int>(threadIdx.x); j < N; j += blockDim.x) labels_c[j] = ignore_index;  // dead tail
-  if (threadIdx.x == 0) *n_live = total;
-}
+// The live-row list itself (row_index, labels_c, pos, n_live) comes from the label front-end kernel in
+// elementwise.cu (launch_compact_labels: stable, one launch, an 8-CTA cluster for long batches).
 
 // xc[j,:] = x[row_index[j],:] for j < n_live; rows up to the next multiple of 128 are zero-filled
 // (GEMMs that contract over rows consume whole 64-row blocks).  One warp per row, 16-byte accesses.
@@ -838,8 +805,8 @@ int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int
   if (N <= 0 || H <= 0 || H % 8 != 0) return fail(B200SFT_ERR_INVALID, "compact_rows: bad shape N=%d H=%d", N, H);
   if (!x || !labels || !xc || !labels_c || !row_index || !pos || !n_live)
     return fail(B200SFT_ERR_INVALID, "null tensor pointer");
-  compact_labels_kernel<<<1, 1024, 0, stream>>>(labels, N, ignore_index, row_index, labels_c, pos, n_live);
-  B200_CUDA_CHECK(cudaGetLastError());
+  const int rc = launch_compact_labels(labels, N, ignore_index, row_index, labels_c, pos, n_live, stream);
+  if (rc != 0) return rc;
   const int warps = 8;
   int grid = (N + warps - 1) / warps;
   if (grid > num_sms() * 8) grid = num_sms() * 8;

@@ -221,7 +221,7 @@ def run_b200(args) -> dict:
     model = build_model(dev, attn, args.layers)
     model.gradient_checkpointing_enable()
     trainable, total = apply_freeze_policy(model)
-    install_fused_head(model)
+    install_fused_head(model, fuse_final_norm=(args.final_norm == "fused"))
     wrapped = model
     hook_state = None
     if world > 1:
@@ -418,7 +418,7 @@ def run_b200(args) -> dict:
                      "packed": "variable-length samples packed to seq_len, flattened [1, B*T], restarting position_ids, "
                                "-100 at sample starts, FA2 varlen"}[args.workload],
             "tokens_per_step": round(tokens_per_step, 1), "valid_label_tokens_per_step": round(valid_dev / args.steps, 1),
-            "skip_ignored_rows": True,
+            "skip_ignored_rows": True, "final_norm": args.final_norm,
             "layers": model.config.num_hidden_layers, "trainable_params": trainable, "total_params": total,
             "l2": "working set (6.2 GB of weights + activations per pass) far exceeds the 126 MB L2; no explicit flush",
             "attention_mask": "None (full-length rows; identical to an all-ones mask)",
@@ -538,6 +538,8 @@ def main():
     ap.add_argument("--attn", default="auto")
     ap.add_argument("--tail", default="b200", choices=["b200", "torch"],
                     help="step tail: this library's fused grad-norm clip + AdamW kernels, or torch's clip_grad_norm_ + fused AdamW")
+    ap.add_argument("--final-norm", default="stock", choices=["stock", "fused"],
+                    help="fused = the decoder's final RMSNorm runs inside the head's row gather (scored rows only)")
     ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink"],
                     help="N>1: gradient hook.  nvlink = this library's fused NVLink reduce+scale kernel over symmetric "
                          "memory; nccl = scale kernel + NCCL allreduce; auto (default) = nvlink when symmetric memory "

@@ -136,12 +136,39 @@ int b200sft_flce_fwd_stats(const void* x, const void* w, const int32_t* labels, 
  */
 int b200sft_compact_rows(const void* x, const int32_t* labels, int N, int H, int ignore_index, void* xc,
                          int32_t* labels_c, int32_t* row_index, int32_t* pos, int32_t* n_live, void* stream);
+/*   The list half alone (row_index, labels_c, pos, n_live as above) from shifted int32 labels. */
+int b200sft_compact_labels(const int32_t* labels, int N, int ignore_index, int32_t* row_index, int32_t* labels_c,
+                           int32_t* pos, int32_t* n_live, void* stream);
 /*   The gather half alone, for a compaction list made by b200sft_label_frontend:
  *   xc[j,:] = x[row_index[j],:] for j < *n_live, zero rows up to the next 128-row boundary. */
 int b200sft_gather_rows(const void* x, const int32_t* row_index, const int32_t* n_live, int N, int H, void* xc,
                         void* stream);
 /*   dx[r,:] = dxc[pos[r],:] when pos[r] >= 0, else 0 (every row of dx is written). */
 int b200sft_scatter_rows(const void* dxc, const int32_t* pos, int N, int H, void* dx, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Final RMSNorm as the producer of the head's X operand.  Replaces, for the rows the loss scores,
+ *   hidden_states = self.norm(hidden_states)   SP/transformers/models/smollm3/modeling_smollm3.py:438
+ *   SmolLM3RMSNorm.forward                      modeling_smollm3.py:271-276
+ * (fp32 statistics; the normalised value rounded to bf16; bf16 multiply by the weight) and its
+ * autograd backward, fused with the row gather / scatter of the compaction above.
+ *   h [N,H] bf16 pre-norm hidden states;  gamma [H] bf16 norm weight;  eps = variance_epsilon
+ *   row_index, n_live: compaction list (b200sft_label_frontend) or both NULL = all N rows in place
+ *   xc [N,H] bf16 out: normalised live rows first, zero rows up to the next 128-row boundary
+ *   rstd [N] fp32 out: rsqrt(mean(h^2) + eps) per (compact) row, saved for the backward
+ */
+int b200sft_rmsnorm_gather(const void* h, const void* gamma, float eps, const int32_t* row_index,
+                           const int32_t* n_live, int N, int H, void* xc, float* rstd, void* stream);
+/*   dyc [N,H] bf16: gradient w.r.t. the normalised (compact) rows, i.e. dX of b200sft_flce_bwd
+ *   pos, row_index, n_live: the compaction maps, or all NULL
+ *   dh [N,H] bf16 out (or NULL): gradient w.r.t. h, zero rows where pos < 0
+ *   dgamma [H] bf16 out (or NULL): gradient w.r.t. gamma (fixed summation order); needs
+ *   b200sft_rmsnorm_bwd_workspace_bytes(H) bytes of workspace */
+size_t b200sft_rmsnorm_bwd_workspace_bytes(int H);
+int b200sft_rmsnorm_scatter_bwd(const void* dyc, const void* h, const void* gamma, const float* rstd,
+                                const int32_t* pos, const int32_t* row_index, const int32_t* n_live, int N,
+                                int H, void* dh, void* dgamma, void* workspace, size_t workspace_bytes,
+                                void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Forward, for callers that cannot allocate.  Has no counterpart in the reference.

@@ -33,7 +33,12 @@ SIGNATURES = {
     "b200sft_compact_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_void_p]),
     "b200sft_label_frontend": (c_int, [c_void_p] * 5 + [c_int, c_int, c_int64] + [c_void_p] * 8),
+    "b200sft_compact_labels": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200sft_gather_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "b200sft_rmsnorm_gather": (c_int, [c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                       c_void_p]),
+    "b200sft_rmsnorm_bwd_workspace_bytes": (c_size_t, [c_int]),
+    "b200sft_rmsnorm_scatter_bwd": (c_int, [c_void_p] * 7 + [c_int, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "b200sft_scatter_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "b200sft_flce_fwd_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int,
                                          c_void_p, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p]),

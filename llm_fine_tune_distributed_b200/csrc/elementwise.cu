@@ -468,6 +468,14 @@ int b200sft_label_frontend(const int64_t* input_ids, const int64_t* labels, cons
   return launch_label_frontend(in, B, T, labels_out, shifted, counts, row_index, labels_c, pos, n_live, stream);
 }
 
+int b200sft_compact_labels(const int32_t* labels, int N, int ignore_index, int32_t* row_index, int32_t* labels_c,
+                           int32_t* pos, int32_t* n_live, void* stream_) {
+  if (N <= 0) return fail(B200SFT_ERR_INVALID, "compact_labels: bad row count %d", N);
+  if (!labels || !row_index || !labels_c || !pos || !n_live) return fail(B200SFT_ERR_INVALID, "null tensor pointer");
+  return launch_compact_labels(labels, N, ignore_index, row_index, labels_c, pos, n_live,
+                               static_cast<cudaStream_t>(stream_));
+}
+
 int b200sft_scale_bf16_inplace(void* buf, size_t n, float scale, void* stream_) {
   if (n == 0) return B200SFT_OK;
   if (!buf) return fail(B200SFT_ERR_INVALID, "null buffer");

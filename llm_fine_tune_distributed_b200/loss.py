@@ -28,7 +28,7 @@ import torch.nn.functional as F
 
 from . import ops
 
-__all__ = ["FusedLMHead", "install_fused_head", "fused_head_armed", "fused_causal_lm_loss", "FusedCELossMixin"]
+__all__ = ["FusedLMHead", "FusedFinalNorm", "install_fused_head", "fused_head_armed", "fused_causal_lm_loss", "FusedCELossMixin"]
 
 
 class FusedLMHead(nn.Module):
@@ -58,6 +58,33 @@ class FusedLMHead(nn.Module):
         return f"in_features={self.in_features}, out_features={self.out_features}, bias=False, fused=True"
 
 
+class FusedFinalNorm(nn.Module):
+    """Stand-in for the decoder's final RMSNorm (``model.model.norm``, modeling_smollm3.py:438) that can be
+    bypassed: armed, it hands the pre-norm hidden states on and the fused loss normalises only the rows it
+    scores (``ops.rmsnorm_gather``).  ``weight`` is the original Parameter under the original name."""
+
+    def __init__(self, norm: nn.Module):
+        super().__init__()
+        self.weight = norm.weight
+        self.variance_epsilon = float(norm.variance_epsilon)
+        self.armed = False
+
+    def forward(self, hidden_states: torch.Tensor) -> torch.Tensor:
+        if self.armed:
+            return hidden_states
+        dtype = hidden_states.dtype   # unarmed: the stock arithmetic (modeling_smollm3.py:271-276)
+        h = hidden_states.to(torch.float32)
+        h = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + self.variance_epsilon)
+        return self.weight * h.to(dtype)
+
+    def extra_repr(self) -> str:
+        return f"{tuple(self.weight.shape)}, eps={self.variance_epsilon}, fused=True"
+
+
+def _final_norm(inner: nn.Module) -> Optional[nn.Module]:
+    return getattr(getattr(inner, "model", None), "norm", None)
+
+
 def _unwrap(model: nn.Module) -> nn.Module:
     while hasattr(model, "module") and isinstance(getattr(model, "module"), nn.Module):
         model = model.module
@@ -65,12 +92,14 @@ def _unwrap(model: nn.Module) -> nn.Module:
 
 
 def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
-                       token_stats: bool = False) -> nn.Module:
+                       token_stats: bool = False, fuse_final_norm: bool = False) -> nn.Module:
     """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model.
 
     ``skip_ignored_rows``: compact away positions labelled -100 (padding, prompt, packed-sample
     boundaries) before the GEMMs.  ``token_stats``: also produce the logits-free token-accuracy
-    count and entropy sum; the latest values are kept in ``model.lm_head.last_stats``."""
+    count and entropy sum; the latest values are kept in ``model.lm_head.last_stats``.
+    ``fuse_final_norm``: also take over the decoder's final RMSNorm (``model.model.norm``) so that only
+    the scored rows are normalised, inside the gather that feeds the head."""
     inner = _unwrap(model)
     head = getattr(inner, "lm_head", None)
     if head is None:
@@ -78,21 +107,33 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, sk
     if not isinstance(head, FusedLMHead):
         head = FusedLMHead(head)
         inner.lm_head = head
-    stock_loss = inner.loss_function
+    if fuse_final_norm:
+        norm = _final_norm(inner)
+        if norm is None or not hasattr(norm, "variance_epsilon") or getattr(norm, "weight", None) is None:
+            raise ValueError("fuse_final_norm needs model.model.norm to be an RMSNorm with weight and variance_epsilon")
+        if not isinstance(norm, FusedFinalNorm):
+            inner.model.norm = FusedFinalNorm(norm)
+    # the model's own loss; kept on the model so that a deep copy (whose patched function still points at the
+    # original's head) can be re-patched without stacking closures
+    stock_loss = getattr(inner, "_b200sft_stock_loss", None) or inner.loss_function
 
     def loss_function(logits, labels, vocab_size=None, **kwargs):
         if head.armed:
+            norm = _final_norm(inner)
+            fused_norm = isinstance(norm, FusedFinalNorm) and norm.armed  # then `logits` are PRE-norm hidden states
             out = fused_causal_lm_loss(logits, head.weight, labels, flags=flags, chunk_cols=chunk_cols,
                                        skip_ignored_rows=skip_ignored_rows, return_stats=token_stats,
-                                       plan=head.plan, **kwargs)
+                                       plan=head.plan, norm_weight=norm.weight if fused_norm else None,
+                                       norm_eps=norm.variance_epsilon if fused_norm else 1e-6, **kwargs)
             if token_stats:
                 out, head.last_stats = out
             return out
         return stock_loss(logits=logits, labels=labels, vocab_size=vocab_size, **kwargs)
 
-    if not getattr(inner, "_b200sft_patched", False):
+    if getattr(inner, "_b200sft_patched", None) != id(inner):
+        inner._b200sft_stock_loss = stock_loss
         inner.loss_function = loss_function
-        inner._b200sft_patched = True
+        inner._b200sft_patched = id(inner)
     return inner
 
 
@@ -103,26 +144,35 @@ def fused_head_armed(model: nn.Module, plan: Optional["ops.LabelPlan"] = None):
     head = _unwrap(model).lm_head
     if not isinstance(head, FusedLMHead):
         raise RuntimeError("call install_fused_head(model) first")
-    prev = head.armed, head.plan
+    norm = _final_norm(_unwrap(model))
+    norm = norm if isinstance(norm, FusedFinalNorm) else None
+    prev = head.armed, head.plan, (norm.armed if norm is not None else False)
     head.armed, head.plan = True, plan
+    if norm is not None:
+        norm.armed = True
     try:
         yield
     finally:
-        head.armed, head.plan = prev
+        head.armed, head.plan = prev[0], prev[1]
+        if norm is not None:
+            norm.armed = prev[2]
 
 
 def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                          num_items_in_batch: Optional[Union[torch.Tensor, int]] = None,
                          ignore_index: int = -100, shift_labels: Optional[torch.Tensor] = None,
                          flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
-                         return_stats: bool = False, plan: Optional["ops.LabelPlan"] = None, **_unused: Any):
+                         return_stats: bool = False, plan: Optional["ops.LabelPlan"] = None,
+                         norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-6, **_unused: Any):
     """``ForCausalLMLoss`` (SP/transformers/loss/loss_utils.py:45-67) on hidden states.
 
     Same arguments and meaning, except that the first argument holds ``[B,T,H]`` hidden states:
     labels are shifted left (or ``shift_labels`` used as given), flattened, and the loss is the
     sum over non-ignored positions divided by ``num_items_in_batch`` -- or the mean over local
     non-ignored positions when that is None.  ``plan``: the :class:`ops.LabelPlan` of ``labels`` when the
-    caller already ran the label front-end (labels built on the device); used as is.
+    caller already ran the label front-end (labels built on the device); used as is.  ``norm_weight`` /
+    ``norm_eps``: ``hidden_states`` are the decoder's output BEFORE its final RMSNorm, which is then applied
+    to the scored rows only (modeling_smollm3.py:438,271-276).
     """
     if hidden_states.dim() == 2:
         hidden_states = hidden_states.unsqueeze(0)
@@ -147,7 +197,9 @@ def fused_causal_lm_loss(hidden_states: torch.Tensor, weight: torch.Tensor, labe
     w = weight if weight.dtype == torch.bfloat16 else weight.to(torch.bfloat16)
     return ops.fused_linear_cross_entropy(h2.contiguous(), w.contiguous(), shifted, num_items_in_batch,
                                           ignore_index=ignore_index, flags=flags, chunk_cols=chunk_cols,
-                                          skip_ignored_rows=skip_ignored_rows, return_stats=return_stats, plan=plan)
+                                          skip_ignored_rows=skip_ignored_rows, return_stats=return_stats, plan=plan,
+                                          norm_weight=None if norm_weight is None else norm_weight.to(torch.bfloat16),
+                                          norm_eps=norm_eps)
 
 
 class FusedCELossMixin:
@@ -168,14 +220,17 @@ class FusedCELossMixin:
     b200sft_chunk_cols: int = 0
     b200sft_skip_ignored_rows: bool = True
     b200sft_token_stats: bool = False  # True: log mean_token_accuracy / entropy like TRL, without logits
+    b200sft_fuse_final_norm: bool = False  # True: the decoder's final RMSNorm runs inside the head's row gather
     b200sft_register_comm_hook: bool = True
     b200sft_nvlink_hook: bool = False  # True (or env B200SFT_COMM=nvlink): the fused NVLink reduce+scale kernel
 
     def _b200sft_prepare(self, model: nn.Module) -> None:
         inner = _unwrap(model)
-        if not isinstance(getattr(inner, "lm_head", None), FusedLMHead):
+        if (not isinstance(getattr(inner, "lm_head", None), FusedLMHead)
+                or getattr(inner, "_b200sft_patched", None) != id(inner)   # e.g. a deep copy of a patched model
+                or (self.b200sft_fuse_final_norm and not isinstance(_final_norm(inner), FusedFinalNorm))):
             install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_cols, self.b200sft_skip_ignored_rows,
-                               self.b200sft_token_stats)
+                               self.b200sft_token_stats, self.b200sft_fuse_final_norm)
         if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)
                 and not getattr(model, "_b200sft_hook", False)):
             import os

@@ -51,7 +51,8 @@ STATS = _Stats()
 
 
 __all__ = [
-    "label_prep", "label_frontend", "gather_rows", "LabelPlan", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
+    "label_prep", "label_frontend", "gather_rows", "compaction_list", "rmsnorm_gather", "rmsnorm_scatter_bwd",
+    "LabelPlan", "flce_forward", "flce_backward", "compact_rows", "scatter_rows", "gemm_bf16", "scale_",
     "scale_cast_f32_to_bf16", "cast_bf16_to_f32", "fused_linear_cross_entropy", "IGNORE_INDEX",
     "FLAG_ROUND_LOGITS_BF16",
 ]
@@ -165,6 +166,76 @@ def gather_rows(x: torch.Tensor, plan: LabelPlan) -> torch.Tensor:
                                       _stream_ptr(x)), "b200sft_gather_rows")
         STATS.kernel_launches += 1
     return xc
+
+
+def compaction_list(labels: torch.Tensor, ignore_index: int = IGNORE_INDEX) -> LabelPlan:
+    """The live-row list of already-shifted int32 ``labels`` as a :class:`LabelPlan` (no counts, no gather)."""
+    _require_cuda(labels)
+    if labels.dtype != torch.int32 or labels.dim() != 1 or not labels.is_contiguous():
+        raise ValueError("labels must be contiguous int32 [N]")
+    N = labels.shape[0]
+    dev = labels.device
+    with torch.cuda.device(dev):
+        row_index, labels_c, pos = (torch.empty(N, dtype=torch.int32, device=dev) for _ in range(3))
+        n_live = torch.zeros((), dtype=torch.int32, device=dev)
+        if N:
+            check(_cabi.load().b200sft_compact_labels(_ptr(labels), N, ignore_index, _ptr(row_index), _ptr(labels_c),
+                                                      _ptr(pos), _ptr(n_live), _stream_ptr(labels)),
+                  "b200sft_compact_labels")
+            STATS.kernel_launches += 1
+    return LabelPlan(labels, None, None, row_index, labels_c, pos, n_live)
+
+
+def rmsnorm_gather(h: torch.Tensor, gamma: torch.Tensor, eps: float, plan: Optional[LabelPlan] = None
+                   ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Final RMSNorm (SP/transformers/models/smollm3/modeling_smollm3.py:271-276) of the rows the loss
+    scores, written compacted: ``xc[j] = gamma * bf16(h[row_index[j]] * rstd[j])``.  Without a plan (or
+    a plan without a list) every row is normalised in place order.  Returns ``(xc [N,H] bf16, rstd [N] fp32)``."""
+    _require_cuda(h, gamma)
+    if h.dtype != torch.bfloat16 or gamma.dtype != torch.bfloat16 or h.dim() != 2 or gamma.shape != (h.shape[1],):
+        raise ValueError("h must be bf16 [N,H] and gamma bf16 [H]")
+    if not (h.is_contiguous() and gamma.is_contiguous()):
+        raise ValueError("h and gamma must be contiguous")
+    N, H = h.shape
+    listed = plan is not None and plan.row_index is not None
+    if listed and plan.row_index.shape != (N,):
+        raise ValueError("label plan does not belong to these rows")
+    with torch.cuda.device(h.device):
+        xc = torch.empty_like(h)
+        rstd = torch.empty(N, dtype=torch.float32, device=h.device)
+        if N:
+            check(_cabi.load().b200sft_rmsnorm_gather(_ptr(h), _ptr(gamma), float(eps),
+                                                      _ptr(plan.row_index) if listed else None,
+                                                      _ptr(plan.n_live) if listed else None, N, H, _ptr(xc), _ptr(rstd),
+                                                      _stream_ptr(h)), "b200sft_rmsnorm_gather")
+            STATS.kernel_launches += 1
+    return xc, rstd
+
+
+def rmsnorm_scatter_bwd(dyc: torch.Tensor, h: torch.Tensor, gamma: torch.Tensor, rstd: torch.Tensor,
+                        plan: Optional[LabelPlan] = None, need_dh: bool = True, need_dgamma: bool = False
+                        ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """Backward of :func:`rmsnorm_gather`: ``dyc`` is the gradient w.r.t. the normalised compact rows
+    (``flce_backward``'s dX); returns ``(dh [N,H] bf16 with zero rows where ignored, dgamma [H] bf16)``."""
+    _require_cuda(dyc, h, gamma, rstd)
+    if dyc.shape != h.shape or dyc.dtype != torch.bfloat16 or not dyc.is_contiguous():
+        raise ValueError("dyc must be contiguous bf16 of h's shape")
+    N, H = h.shape
+    listed = plan is not None and plan.row_index is not None
+    lib = _cabi.load()
+    with torch.cuda.device(h.device):
+        dh = torch.empty_like(h) if need_dh else None
+        dgamma = torch.zeros_like(gamma) if need_dgamma else None
+        if N and (need_dh or need_dgamma):
+            ws_bytes = lib.b200sft_rmsnorm_bwd_workspace_bytes(H) if need_dgamma else 0
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=h.device) if ws_bytes else None
+            check(lib.b200sft_rmsnorm_scatter_bwd(_ptr(dyc), _ptr(h), _ptr(gamma), _ptr(rstd),
+                                                  _ptr(plan.pos) if listed else None,
+                                                  _ptr(plan.row_index) if listed else None,
+                                                  _ptr(plan.n_live) if listed else None, N, H, _ptr(dh), _ptr(dgamma),
+                                                  _ptr(ws), ws_bytes, _stream_ptr(h)), "b200sft_rmsnorm_scatter_bwd")
+            STATS.kernel_launches += (1 if need_dh else 0) + (2 if need_dgamma else 0)
+    return dh, dgamma
 
 
 def _check_flce_inputs(x: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> Tuple[int, int, int]:
@@ -422,10 +493,19 @@ def _(x, w, labels, lse, grad_out, scale, denom, ignore_index, flags, chunk_cols
 class _FusedLinearCrossEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, labels, scale, denom, reduction_mean, ignore_index, flags, chunk_cols, skip_ignored,
-                with_stats, plan):
-        pos = n_rows = None
+                with_stats, plan, norm_weight, norm_eps):
+        pos = n_rows = rstd = None
         xk, lk = x, labels
-        if skip_ignored and plan is not None and plan.row_index is not None:
+        listed = plan is not None and plan.row_index is not None
+        if norm_weight is not None:  # x holds PRE-norm rows: the final RMSNorm rides on the gather
+            if skip_ignored and not listed:
+                plan, listed = compaction_list(labels, ignore_index), True
+            if not skip_ignored:
+                plan, listed = None, False
+            xk, rstd = rmsnorm_gather(x, norm_weight, norm_eps, plan)
+            if listed:
+                lk, pos, n_rows = plan.labels_c, plan.pos, plan.n_live
+        elif skip_ignored and listed:
             xk, lk, pos, n_rows = gather_rows(x, plan), plan.labels_c, plan.pos, plan.n_live  # list already made
         elif skip_ignored:  # run every GEMM on the live rows only
             xk, lk, _row_index, pos, n_rows = compact_rows(x, labels, ignore_index)
@@ -433,26 +513,37 @@ class _FusedLinearCrossEntropy(torch.autograd.Function):
             xk, w, lk, scale, denom, reduction_mean, ignore_index, flags, n_rows, with_stats)
         # reduction="mean" divides by the local valid count; backward takes it as a device scalar
         bwd_denom = n_valid if reduction_mean else denom
-        ctx.save_for_backward(xk, w, lk, lse, bwd_denom, pos, n_rows)
+        fused_norm = norm_weight is not None  # then also: pre-norm rows, weight, 1/rms and the list, for its backward
+        ctx.save_for_backward(xk, w, lk, lse, bwd_denom, pos, n_rows, x if fused_norm else None, norm_weight, rstd,
+                              plan.row_index if (fused_norm and listed) else None)
         ctx.scale, ctx.ignore_index, ctx.flags, ctx.chunk_cols = scale, ignore_index, flags, chunk_cols
+        ctx.fused_norm = fused_norm
         ctx.mark_non_differentiable(n_valid, n_correct, entropy_sum)
         return loss, n_valid, n_correct, entropy_sum
 
     @staticmethod
     def backward(ctx, grad_loss, *_unused):
-        xk, w, lk, lse, bwd_denom, pos, n_rows = ctx.saved_tensors
+        xk, w, lk, lse, bwd_denom, pos, n_rows, h, gamma, rstd, row_index = ctx.saved_tensors
         need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        need_dgamma = ctx.fused_norm and ctx.needs_input_grad[12]
         dx, dw = torch.ops.b200sft.flce_bwd(xk, w, lk, lse, grad_loss, ctx.scale, bwd_denom, ctx.ignore_index,
-                                            ctx.flags, ctx.chunk_cols, n_rows, need_dx, need_dw)
-        dx = None if not need_dx else (scatter_rows(dx, pos) if pos is not None else dx)
-        return dx, (dw if need_dw else None), None, None, None, None, None, None, None, None, None, None
+                                            ctx.flags, ctx.chunk_cols, n_rows, need_dx or need_dgamma, need_dw)
+        dgamma = None
+        if ctx.fused_norm:
+            plan = LabelPlan(None, None, None, row_index, lk, pos, n_rows) if row_index is not None else None
+            dx, dgamma = rmsnorm_scatter_bwd(dx, h, gamma, rstd, plan, need_dx, need_dgamma)
+        else:
+            dx = None if not need_dx else (scatter_rows(dx, pos) if pos is not None else dx)
+        return (dx, (dw if need_dw else None), None, None, None, None, None, None, None, None, None, None,
+                dgamma, None)
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shifted_labels: torch.Tensor,
                                num_items_in_batch: Optional[torch.Tensor] = None, scale: float = 1.0,
                                ignore_index: int = IGNORE_INDEX, flags: int = 0, chunk_cols: int = 0,
                                skip_ignored_rows: bool = False, return_stats: bool = False,
-                               plan: Optional[LabelPlan] = None):
+                               plan: Optional[LabelPlan] = None, norm_weight: Optional[torch.Tensor] = None,
+                               norm_eps: float = 1e-6):
     """Differentiable ``cross_entropy(hidden @ weight.T, shifted_labels)`` without the logits.
 
     ``num_items_in_batch`` None -> mean over local valid rows (``reduction="mean"``), else the
@@ -463,6 +554,9 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shift
     ``stats = {"n_valid", "n_correct", "entropy_sum"}`` device scalars (token accuracy and mean
     entropy are n_correct / n_valid and entropy_sum / n_valid).  ``plan``: the :class:`LabelPlan`
     ``shifted_labels`` came from; its compaction list is then reused instead of being rebuilt.
+    ``norm_weight`` (bf16 [H]) / ``norm_eps``: ``hidden`` holds the rows BEFORE the model's final RMSNorm
+    (modeling_smollm3.py:438); the norm is applied to the scored rows while they are gathered, and its
+    backward (dX and the weight's gradient) is part of this op's backward.
     """
     denom = None
     if num_items_in_batch is not None:
@@ -471,7 +565,7 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, shift
         denom = num_items_in_batch.to(device=hidden.device, dtype=torch.int64).reshape(())
     loss, n_valid, n_correct, entropy_sum = _FusedLinearCrossEntropy.apply(
         hidden, weight, shifted_labels, float(scale), denom, num_items_in_batch is None, ignore_index, flags,
-        chunk_cols, bool(skip_ignored_rows), bool(return_stats), plan)
+        chunk_cols, bool(skip_ignored_rows), bool(return_stats), plan, norm_weight, float(norm_eps))
     if return_stats:
         return loss, {"n_valid": n_valid, "n_correct": n_correct, "entropy_sum": entropy_sum}
     return loss

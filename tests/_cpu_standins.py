@@ -30,7 +30,9 @@ def label_frontend(input_ids=None, labels=None, attention_mask=None, completion_
 
 def fused_linear_cross_entropy(hidden, weight, shifted_labels, num_items_in_batch=None, scale=1.0,
                                ignore_index=-100, flags=0, chunk_cols=0, skip_ignored_rows=False, return_stats=False,
-                               plan=None):
+                               plan=None, norm_weight=None, norm_eps=1e-6):
+    if norm_weight is not None:
+        hidden = oracle.rms_norm(hidden, norm_weight, norm_eps)
     n = None if num_items_in_batch is None else float(num_items_in_batch)
     loss = oracle.lm_head_ce(hidden, weight, shifted_labels.long(), n, ignore_index) * scale
     if return_stats:

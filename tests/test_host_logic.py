@@ -186,6 +186,41 @@ def test_compute_loss_seam_takes_a_label_plan(tiny, monkeypatch):
         seam.compute_loss(tiny, {"input_ids": ids, "labels": labels, "b200sft_plan": wrong}, num_items_in_batch=n)
 
 
+def test_fused_final_norm_keeps_names_and_the_seam_result(tiny, monkeypatch):
+    """model.model.norm swapped for the bypassable stand-in: same state-dict keys, same unarmed forward, and
+    the armed compute_loss (kernels replaced by the oracle stand-ins) still reproduces the golden values
+    of the real Trainer.compute_loss -- now with the norm applied inside the loss."""
+    import copy
+
+    from llm_fine_tune_distributed_b200 import FusedCELossMixin, install_fused_head
+    from llm_fine_tune_distributed_b200.loss import FusedFinalNorm
+
+    _cpu_standins.install(monkeypatch)
+    d = np.load(os.path.join(G, "smollm3_tiny_step.npz"))
+    m = copy.deepcopy(tiny)
+    keys = set(m.state_dict().keys())
+    ids = torch.from_numpy(d["input_ids_0"])
+    with torch.no_grad():
+        before = m(ids).logits
+    install_fused_head(m, fuse_final_norm=True)
+    assert isinstance(m.model.norm, FusedFinalNorm) and set(m.state_dict().keys()) == keys
+    assert m.model.norm.weight is dict(m.named_parameters())["model.norm.weight"]
+    with torch.no_grad():
+        assert torch.equal(m(ids).logits, before)
+
+    class Seam(FusedCELossMixin):
+        num_processes = 2
+        model_accepts_loss_kwargs = True
+        args = None
+        b200sft_fuse_final_norm = True
+
+    loss = Seam().compute_loss(m, {"input_ids": ids, "labels": torch.from_numpy(d["labels_0"])},
+                               num_items_in_batch=torch.tensor(int(d["num_items"])))
+    ref = float(d["compute_loss_0"])
+    assert abs(float(loss) - ref) <= 1e-6 * abs(ref)
+    assert not m.model.norm.armed and not m.lm_head.armed
+
+
 def test_patched_model_saves_and_reloads_as_stock(tiny, tmp_path):
     """The head swap must not leak into checkpoints: save_pretrained on the patched model, then a
     stock from_pretrained, gives the same logits (training.py:309-312 saves the best model this way)."""

@@ -80,3 +80,23 @@ def test_allreduce_hook_bucket_matches_default_hook():
     for r in range(world):
         got = oracle.allreduce_hook_bucket(buckets[r].clone(), world, lambda t: t.copy_(total))
         assert torch.equal(got.float(), torch.from_numpy(d[f"result_rank{r}"]))
+
+
+def test_rms_norm_restatement_is_the_transformers_module():
+    """oracle.rms_norm against the real SmolLM3RMSNorm (forward and autograd), bit for bit."""
+    from transformers.models.smollm3.modeling_smollm3 import SmolLM3RMSNorm
+
+    torch.manual_seed(0)
+    mod = SmolLM3RMSNorm(96, eps=1e-6).to(torch.bfloat16)
+    with torch.no_grad():
+        mod.weight.add_(0.1 * torch.randn(96).to(torch.bfloat16))
+    x = (torch.randn(5, 7, 96) * 2).to(torch.bfloat16)
+    a = x.clone().requires_grad_(True)
+    b = x.clone().requires_grad_(True)
+    w = mod.weight.detach().clone().requires_grad_(True)
+    ya, yb = mod(a), oracle.rms_norm(b, w, mod.variance_epsilon)
+    assert torch.equal(ya, yb)
+    g = torch.randn_like(ya)
+    ya.backward(g)
+    yb.backward(g)
+    assert torch.equal(a.grad, b.grad) and torch.equal(mod.weight.grad, w.grad)

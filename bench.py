@@ -221,7 +221,7 @@ def run_b200(args) -> dict:
     model = build_model(dev, attn, args.layers)
     model.gradient_checkpointing_enable()
     trainable, total = apply_freeze_policy(model)
-    install_fused_head(model, fuse_final_norm=(args.final_norm == "fused"))
+    install_fused_head(model, fuse_final_norm=(args.final_norm == "fused"))  # True: must apply, else raise
     wrapped = model
     hook_state = None
     if world > 1:
@@ -538,7 +538,7 @@ def main():
     ap.add_argument("--attn", default="auto")
     ap.add_argument("--tail", default="b200", choices=["b200", "torch"],
                     help="step tail: this library's fused grad-norm clip + AdamW kernels, or torch's clip_grad_norm_ + fused AdamW")
-    ap.add_argument("--final-norm", default="stock", choices=["stock", "fused"],
+    ap.add_argument("--final-norm", default="fused", choices=["stock", "fused"],
                     help="fused = the decoder's final RMSNorm runs inside the head's row gather (scored rows only)")
     ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink"],
                     help="N>1: gradient hook.  nvlink = this library's fused NVLink reduce+scale kernel over symmetric "

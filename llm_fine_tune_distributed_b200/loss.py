@@ -85,6 +85,23 @@ def _final_norm(inner: nn.Module) -> Optional[nn.Module]:
     return getattr(getattr(inner, "model", None), "norm", None)
 
 
+def _norm_is_fusable(norm: Optional[nn.Module]) -> bool:
+    """True when ``norm`` computes exactly what the fused kernels restate (weight * bf16(x * rsqrt(mean(x^2) + eps)),
+    modeling_smollm3.py:271-276): checked on a probe input instead of trusting the class name."""
+    if isinstance(norm, FusedFinalNorm):
+        return True
+    w = getattr(norm, "weight", None)
+    if norm is None or w is None or not hasattr(norm, "variance_epsilon") or w.dim() != 1 or w.dtype != torch.bfloat16:
+        return False
+    try:
+        with torch.no_grad():
+            g = torch.Generator(device="cpu").manual_seed(0)
+            x = (torch.randn(4, w.shape[0], generator=g) * 2).to(device=w.device, dtype=w.dtype)
+            return bool(torch.equal(norm(x), FusedFinalNorm(norm)(x)))
+    except Exception:
+        return False
+
+
 def _unwrap(model: nn.Module) -> nn.Module:
     while hasattr(model, "module") and isinstance(getattr(model, "module"), nn.Module):
         model = model.module
@@ -92,14 +109,15 @@ def _unwrap(model: nn.Module) -> nn.Module:
 
 
 def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, skip_ignored_rows: bool = True,
-                       token_stats: bool = False, fuse_final_norm: bool = False) -> nn.Module:
+                       token_stats: bool = False, fuse_final_norm: Optional[bool] = None) -> nn.Module:
     """Patch a HF causal-LM in place (idempotent).  Returns the (unwrapped) model.
 
     ``skip_ignored_rows``: compact away positions labelled -100 (padding, prompt, packed-sample
     boundaries) before the GEMMs.  ``token_stats``: also produce the logits-free token-accuracy
     count and entropy sum; the latest values are kept in ``model.lm_head.last_stats``.
     ``fuse_final_norm``: also take over the decoder's final RMSNorm (``model.model.norm``) so that only
-    the scored rows are normalised, inside the gather that feeds the head."""
+    the scored rows are normalised, inside the gather that feeds the head.  None (default) = when that
+    module is a bf16 RMSNorm computing exactly the reference's formula; True = required (raises otherwise)."""
     inner = _unwrap(model)
     head = getattr(inner, "lm_head", None)
     if head is None:
@@ -107,12 +125,14 @@ def install_fused_head(model: nn.Module, flags: int = 0, chunk_cols: int = 0, sk
     if not isinstance(head, FusedLMHead):
         head = FusedLMHead(head)
         inner.lm_head = head
-    if fuse_final_norm:
+    if fuse_final_norm is not False:
         norm = _final_norm(inner)
-        if norm is None or not hasattr(norm, "variance_epsilon") or getattr(norm, "weight", None) is None:
-            raise ValueError("fuse_final_norm needs model.model.norm to be an RMSNorm with weight and variance_epsilon")
-        if not isinstance(norm, FusedFinalNorm):
-            inner.model.norm = FusedFinalNorm(norm)
+        if _norm_is_fusable(norm):
+            if not isinstance(norm, FusedFinalNorm):
+                inner.model.norm = FusedFinalNorm(norm)
+        elif fuse_final_norm:
+            raise ValueError("fuse_final_norm needs model.model.norm to be a bf16 RMSNorm computing "
+                             "weight * (x * rsqrt(mean(x^2) + variance_epsilon)).to(bf16)")
     # the model's own loss; kept on the model so that a deep copy (whose patched function still points at the
     # original's head) can be re-patched without stacking closures
     stock_loss = getattr(inner, "_b200sft_stock_loss", None) or inner.loss_function
@@ -220,7 +240,7 @@ class FusedCELossMixin:
     b200sft_chunk_cols: int = 0
     b200sft_skip_ignored_rows: bool = True
     b200sft_token_stats: bool = False  # True: log mean_token_accuracy / entropy like TRL, without logits
-    b200sft_fuse_final_norm: bool = False  # True: the decoder's final RMSNorm runs inside the head's row gather
+    b200sft_fuse_final_norm: Optional[bool] = None  # final RMSNorm inside the head's row gather: None = when it applies
     b200sft_register_comm_hook: bool = True
     b200sft_nvlink_hook: bool = False  # True (or env B200SFT_COMM=nvlink): the fused NVLink reduce+scale kernel
 
@@ -228,7 +248,7 @@ class FusedCELossMixin:
         inner = _unwrap(model)
         if (not isinstance(getattr(inner, "lm_head", None), FusedLMHead)
                 or getattr(inner, "_b200sft_patched", None) != id(inner)   # e.g. a deep copy of a patched model
-                or (self.b200sft_fuse_final_norm and not isinstance(_final_norm(inner), FusedFinalNorm))):
+                or (self.b200sft_fuse_final_norm and not isinstance(_final_norm(inner), FusedFinalNorm))):  # required
             install_fused_head(inner, self.b200sft_flags, self.b200sft_chunk_cols, self.b200sft_skip_ignored_rows,
                                self.b200sft_token_stats, self.b200sft_fuse_final_norm)
         if (self.b200sft_register_comm_hook and isinstance(model, nn.parallel.DistributedDataParallel)

@@ -337,7 +337,8 @@ class MiniSFTTrainer(FusedCELossMixin):
         self.num_processes = self.world
         self.model_accepts_loss_kwargs = True  # SmolLM3 forward takes **kwargs (trainer.py:1925-1927)
         self.loss_impl = loss_impl
-        self.b200sft_fuse_final_norm = os.getenv("FUSE_FINAL_NORM", "0") == "1"  # final RMSNorm inside the head's gather
+        env = os.getenv("FUSE_FINAL_NORM")  # final RMSNorm inside the head's gather: unset = when it applies, 0 / 1 = off / required
+        self.b200sft_fuse_final_norm = None if env is None else env == "1"
         self.model = model.to(self.device)
         if args.gradient_checkpointing and hasattr(self.model, "gradient_checkpointing_enable"):
             self.model.gradient_checkpointing_enable()

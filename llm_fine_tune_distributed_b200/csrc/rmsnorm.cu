@@ -4,9 +4,10 @@
 // cast, mul by weight -- SP/transformers/models/smollm3/modeling_smollm3.py:271-276) and the loss
 // then ignores every row labelled -100.  Here the norm rides on the gather the compaction does
 // anyway: one pass reads the live pre-norm rows and writes the normalised compact rows; the backward
-// rides on the scatter.  HBM-bound: one warp per row, 16-byte accesses, the row is re-read from L1
-// for the second pass.  Rounding points follow the reference: fp32 statistics, the normalised value
-// rounded to bf16, then a bf16 multiply by the weight.
+// rides on the scatter.  HBM-bound: one warp per row, 16-byte accesses; rows of 1024 / 2048 elements
+// stay in registers between the two passes, other widths re-read the row from L1.  Rounding points
+// follow the reference: fp32 statistics, the normalised value rounded to bf16, then a bf16 multiply
+// by the weight.
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -83,6 +84,104 @@ rmsnorm_gather_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* 
       dst[v] = pack8(y);
     }
     if (lane == 0) rstd[j] = r;
+  }
+}
+
+// Same, for H = 256 * VPL: the lane's VPL vectors of the row stay in registers, so the row is read once
+// and all its loads are in flight together.  Same summation order as the generic kernel (same bits).
+template <int VPL>
+__global__ void __launch_bounds__(NORM_WARPS * 32)
+rmsnorm_gather_reg_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ gamma, float eps,
+                          const int32_t* __restrict__ row_index, const int32_t* __restrict__ n_live, int N,
+                          __nv_bfloat16* __restrict__ xc, float* __restrict__ rstd) {
+  constexpr int H = VPL * 256;
+  const int live = n_live ? min(max(*n_live, 0), N) : N;
+  const int padded = min((live + 127) / 128 * 128, N);
+  const int lane = threadIdx.x & 31;
+  const uint4* g4 = reinterpret_cast<const uint4*>(gamma);
+  for (int j = blockIdx.x * NORM_WARPS + (threadIdx.x >> 5); j < padded; j += gridDim.x * NORM_WARPS) {
+    uint4* dst = reinterpret_cast<uint4*>(xc + static_cast<size_t>(j) * H);
+    if (j >= live) {
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) dst[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const int src_row = row_index ? row_index[j] : j;
+    const uint4* src = reinterpret_cast<const uint4*>(h + static_cast<size_t>(src_row) * H);
+    uint4 xv[VPL];
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) xv[k] = src[lane + 32 * k];
+    float ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      float x[8];
+      unpack8(xv[k], x);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss = fmaf(x[e], x[e], ss);
+    }
+    const float r = rsqrtf(warp_sum(ss) * (1.f / static_cast<float>(H)) + eps);
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      float x[8], g[8], y[8];
+      unpack8(xv[k], x);
+      unpack8(g4[lane + 32 * k], g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) y[e] = g[e] * round_bf16(x[e] * r);
+      dst[lane + 32 * k] = pack8(y);
+    }
+    if (lane == 0) rstd[j] = r;
+  }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(NORM_WARPS * 32)
+rmsnorm_scatter_bwd_reg_kernel(const __nv_bfloat16* __restrict__ dyc, const __nv_bfloat16* __restrict__ h,
+                               const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ rstd,
+                               const int32_t* __restrict__ pos, int N, __nv_bfloat16* __restrict__ dh) {
+  constexpr int H = VPL * 256;
+  const int lane = threadIdx.x & 31;
+  const uint4* g4 = reinterpret_cast<const uint4*>(gamma);
+  for (int row = blockIdx.x * NORM_WARPS + (threadIdx.x >> 5); row < N; row += gridDim.x * NORM_WARPS) {
+    uint4* dst = reinterpret_cast<uint4*>(dh + static_cast<size_t>(row) * H);
+    const int j = pos ? pos[row] : row;
+    if (j < 0) {
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) dst[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const uint4* dy4 = reinterpret_cast<const uint4*>(dyc + static_cast<size_t>(j) * H);
+    const uint4* h4 = reinterpret_cast<const uint4*>(h + static_cast<size_t>(row) * H);
+    uint4 dv[VPL], xv[VPL];
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      dv[k] = dy4[lane + 32 * k];
+      xv[k] = h4[lane + 32 * k];
+    }
+    const float r = rstd[j];
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      float dy[8], x[8], g[8];
+      unpack8(dv[k], dy);
+      unpack8(xv[k], x);
+      unpack8(g4[lane + 32 * k], g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc = fmaf(round_bf16(dy[e] * g[e]), x[e] * r, acc);
+    }
+    const float c = warp_sum(acc) * (1.f / static_cast<float>(H));
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      float dy[8], x[8], g[8], o[8];
+      unpack8(dv[k], dy);
+      unpack8(xv[k], x);
+      unpack8(g4[lane + 32 * k], g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float n = x[e] * r;
+        o[e] = r * (round_bf16(dy[e] * g[e]) - n * c);
+      }
+      dst[lane + 32 * k] = pack8(o);
+    }
   }
 }
 
@@ -207,9 +306,15 @@ int b200sft_rmsnorm_gather(const void* h, const void* gamma, float eps, const in
     return fail(B200SFT_ERR_INVALID, "row_index and n_live must be given together");
   if (!aligned16(h) || !aligned16(gamma) || !aligned16(xc))
     return fail(B200SFT_ERR_INVALID, "rmsnorm_gather needs 16-byte aligned tensors");
-  rmsnorm_gather_kernel<<<row_grid(N), NORM_WARPS * 32, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(gamma), eps, row_index, n_live, N, H,
-      static_cast<__nv_bfloat16*>(xc), rstd);
+  const auto* hp = static_cast<const __nv_bfloat16*>(h);
+  const auto* gp = static_cast<const __nv_bfloat16*>(gamma);
+  auto* xp = static_cast<__nv_bfloat16*>(xc);
+  const int grid = row_grid(N), threads = NORM_WARPS * 32;
+  switch (H) {  // rows of 256 * VPL elements stay in registers
+    case 1024: rmsnorm_gather_reg_kernel<4><<<grid, threads, 0, stream>>>(hp, gp, eps, row_index, n_live, N, xp, rstd); break;
+    case 2048: rmsnorm_gather_reg_kernel<8><<<grid, threads, 0, stream>>>(hp, gp, eps, row_index, n_live, N, xp, rstd); break;
+    default: rmsnorm_gather_kernel<<<grid, threads, 0, stream>>>(hp, gp, eps, row_index, n_live, N, H, xp, rstd);
+  }
   B200_CUDA_CHECK(cudaGetLastError());
   return B200SFT_OK;
 }
@@ -232,9 +337,16 @@ int b200sft_rmsnorm_scatter_bwd(const void* dyc, const void* h, const void* gamm
   if (!aligned16(dyc) || !aligned16(h) || !aligned16(gamma) || (dh && !aligned16(dh)))
     return fail(B200SFT_ERR_INVALID, "rmsnorm_scatter_bwd needs 16-byte aligned tensors");
   if (dh) {
-    rmsnorm_scatter_bwd_kernel<<<row_grid(N), NORM_WARPS * 32, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(dyc), static_cast<const __nv_bfloat16*>(h),
-        static_cast<const __nv_bfloat16*>(gamma), rstd, pos, N, H, static_cast<__nv_bfloat16*>(dh));
+    const auto* dp = static_cast<const __nv_bfloat16*>(dyc);
+    const auto* hp = static_cast<const __nv_bfloat16*>(h);
+    const auto* gp = static_cast<const __nv_bfloat16*>(gamma);
+    auto* op = static_cast<__nv_bfloat16*>(dh);
+    const int grid = row_grid(N), threads = NORM_WARPS * 32;
+    switch (H) {
+      case 1024: rmsnorm_scatter_bwd_reg_kernel<4><<<grid, threads, 0, stream>>>(dp, hp, gp, rstd, pos, N, op); break;
+      case 2048: rmsnorm_scatter_bwd_reg_kernel<8><<<grid, threads, 0, stream>>>(dp, hp, gp, rstd, pos, N, op); break;
+      default: rmsnorm_scatter_bwd_kernel<<<grid, threads, 0, stream>>>(dp, hp, gp, rstd, pos, N, H, op);
+    }
     B200_CUDA_CHECK(cudaGetLastError());
   }
   if (dgamma) {

@@ -54,7 +54,7 @@ def main():
     ap.add_argument("--no-torch", action="store_true")
     ap.add_argument("--cpu-tokens", type=int, default=0,
                     help="also time the reference head + CE forward/backward on the host cores at this many tokens "
-                         "(oracle.lm_head_ce_with_grads: F.linear -> .float() -> F.cross_entropy + autograd, bf16)")
+                         "(the same torch path as the GPU comparison: F.linear -> .float() -> F.cross_entropy + autograd, bf16)")
     ap.add_argument("--kernel-times", action="store_true", help="also print per-kernel device times (torch.profiler)")
     ap.add_argument("--skip-ignored", action="store_true", help="compact away ignore_index rows first (valid-row compaction)")
     args = ap.parse_args()
@@ -67,15 +67,18 @@ def main():
     if args.cpu_tokens > 0:
         import time
 
-        from oracle import sft_oracle as oracle
+        def cpu_head_ce(xh, wh, lh, n_items):  # the torch comparison path below, on the host cores
+            xh, wh = xh.clone().requires_grad_(True), wh.clone().requires_grad_(True)
+            logits = torch.nn.functional.linear(xh, wh).float()
+            (torch.nn.functional.cross_entropy(logits, lh, ignore_index=-100, reduction="sum") / n_items).backward()
 
         n = args.cpu_tokens
         xc = torch.randn(n, H, generator=torch.Generator().manual_seed(0)).to(torch.bfloat16)
         wc = w.cpu()
         lc = torch.randint(0, V, (n,), generator=torch.Generator().manual_seed(2))
-        oracle.lm_head_ce_with_grads(xc[:64], wc, lc[:64], 64.0)      # warm the thread pool
+        cpu_head_ce(xc[:64], wc, lc[:64], 64.0)      # warm the thread pool
         t0 = time.perf_counter()
-        oracle.lm_head_ce_with_grads(xc, wc, lc, float(n))
+        cpu_head_ce(xc, wc, lc, float(n))
         dt = time.perf_counter() - t0
         print(json.dumps({"cpu_reference_head_ce": {"tokens": n, "seconds_fwd_bwd": round(dt, 3),
                                                     "tflops_6NHV": round(6.0 * n * H * V / dt / 1e12, 3),

@@ -6,7 +6,7 @@ set -u
 mkdir -p gpurun_out
 MB="python benchmarks/flce_microbench.py --tokens 8192 --masked 0.0 --iters 2 --warmup 1 --no-torch"
 BENCH="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-clocks"
-OURS='regex:gemm_tcgen05|flce_|label_prep|label_frontend|gather_rows|scatter_rows|dx_combine|grad_sumsq|grad_norm_finish|adamw_clip|scale_bf16|allreduce_scale'
+OURS='regex:gemm_tcgen05|flce_|label_prep|label_frontend|gather_rows|scatter_rows|rmsnorm_|dx_combine|grad_sumsq|grad_norm_finish|adamw_clip|scale_bf16|allreduce_scale'
 
 # usage: profile_gpu.sh [micro|step|all]   (default: micro)
 WHAT="${1:-micro}"

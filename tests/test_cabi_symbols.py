@@ -75,3 +75,19 @@ def test_python_ops_refuse_cpu_tensors():
     with pytest.raises(B200SftError):
         ops.fused_linear_cross_entropy(torch.zeros(8, 8, dtype=torch.bfloat16), torch.zeros(8, 8, dtype=torch.bfloat16),
                                        torch.zeros(8, dtype=torch.int32))
+
+
+def test_product_code_never_imports_the_oracle():
+    """oracle/ is test infrastructure: only tests/, __graft_entry__.smoke() and bench.py's CPU legs may use
+    it.  The package, the benchmarks and the examples must not."""
+    import pathlib
+    import re
+
+    root = pathlib.Path(__file__).resolve().parent.parent
+    pat = re.compile(r"^\s*(from\s+oracle\b|import\s+oracle\b)", re.M)
+    offenders = [str(p.relative_to(root))
+                 for d in ("llm_fine_tune_distributed_b200", "benchmarks", "examples")
+                 for p in (root / d).rglob("*.py") if pat.search(p.read_text())]
+    assert not offenders, offenders
+    for src in (root / "llm_fine_tune_distributed_b200" / "csrc").glob("*.cu*"):
+        assert "oracle" not in src.read_text(), src.name

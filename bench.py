@@ -430,7 +430,7 @@ def run_b200(args) -> dict:
                 "last_loss": last_loss},
         "gpu_launches": launches,
         "roofline": {
-            "kernel": "gemm_tcgen05_2cta_kernel<FwdSoftmaxEpi> (+ label compaction, row merge and loss reduce: the whole "
+            "kernel": "gemm_tcgen05_2cta_kernel<FwdSoftmaxEpi> (+ target-logit memset, row merge and loss reduce: the whole "
                       f"b200sft_flce_fwd call), N={N} x H={H} x V={V}",
             "bound": "tensor", "achieved": round(achieved, 1), "peak": peaks["sustained"], "unit": "TFLOP/s",
             "frac": round(achieved / peaks["sustained"], 4), "traffic": traffic,

@@ -58,3 +58,39 @@ def test_padded_completion_only_labels():
     np.testing.assert_array_equal(got["labels_c"][: live.size], shifted[live])
     assert (got["labels_c"][live.size:] == -100).all() and got["n_live"] == live.size
     assert (got["pos"][live] == np.arange(live.size)).all() and (np.delete(got["pos"], live) == -1).all()
+
+
+def test_frontend_restatement_invariants_hypothesis():
+    """Properties any label front-end output must have, on random shapes and masks (the size-independent
+    checks the GPU test repeats at full size through bit-equality with this restatement)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(B=st.integers(1, 6), T=st.integers(1, 70), seed=st.integers(0, 2 ** 31 - 1),
+           use_att=st.booleans(), use_comp=st.booleans(), use_pos=st.booleans())
+    def check(B, T, seed, use_att, use_comp, use_pos):
+        rng = np.random.default_rng(seed)
+        ids = rng.integers(0, 1000, size=(B, T))
+        att = (rng.random((B, T)) > 0.2).astype(np.int64) if use_att else None
+        comp = (rng.random((B, T)) > 0.5).astype(np.int64) if use_comp else None
+        posid = np.where(rng.random((B, T)) < 0.15, 0, 1 + rng.integers(0, 9, size=(B, T))) if use_pos else None
+        r = oracle.label_frontend_numpy(ids, None, att, comp, posid)
+        lab, sh = r["labels"], r["shifted"].reshape(B, T)
+        assert (sh[:, -1] == -100).all() and (sh[:, :-1] == lab[:, 1:]).all()           # the shift
+        assert r["counts"] == (int((lab != -100).sum()), int((sh != -100).sum()))
+        assert r["counts"][1] == r["n_live"] <= r["counts"][0]                              # shifting only loses labels
+        live = r["row_index"]
+        assert (np.diff(live) > 0).all()                                                    # stable order
+        assert (r["pos"][live] == np.arange(live.size)).all() and (r["pos"] >= -1).all()   # inverse maps
+        assert int((r["pos"] >= 0).sum()) == r["n_live"]
+        assert (r["labels_c"][: r["n_live"]] != -100).all() and (r["labels_c"][r["n_live"]:] == -100).all()
+        # every mask only removes labels
+        assert ((lab == ids) | (lab == -100)).all()
+        if att is not None:
+            assert (lab[att == 0] == -100).all()
+        if comp is not None:
+            assert (lab[comp == 0] == -100).all()
+        if posid is not None:
+            assert (lab[posid == 0] == -100).all()
+
+    check()

@@ -195,6 +195,10 @@ def window_tokens(window) -> tuple:
 # this repository's arm
 # ------------------------------------------------------------------------------------------
 def run_b200(args) -> dict:
+    """This repository's arm (``--impl b200``) and, with ``--impl stock``, the same step on the stock GPU path the
+    reference would take on this box: transformers' lm_head + ForCausalLMLoss (logits materialised), torch's
+    clip_grad_norm_ + fused AdamW, DDP's built-in allreduce -- none of this library's kernels."""
+    stock = args.impl == "stock"
     from llm_fine_tune_distributed_b200.comm_hook import (B200HookState, B200NvlinkState, b200_allreduce_hook,
                                                           b200_nvlink_allreduce_hook)
     from llm_fine_tune_distributed_b200.loss import FusedCELossMixin, install_fused_head
@@ -221,12 +225,16 @@ def run_b200(args) -> dict:
     model = build_model(dev, attn, args.layers)
     model.gradient_checkpointing_enable()
     trainable, total = apply_freeze_policy(model)
-    install_fused_head(model, fuse_final_norm=(args.final_norm == "fused"))  # True: must apply, else raise
+    if not stock:
+        install_fused_head(model, fuse_final_norm=(args.final_norm == "fused"))  # True: must apply, else raise
     wrapped = model
     hook_state = None
     if world > 1:
         wrapped = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], bucket_cap_mb=50,
                                                             find_unused_parameters=False)
+    if world > 1 and stock:
+        args.comm = "ddp-default"
+    elif world > 1:
         comm = os.environ.get("B200SFT_COMM", args.comm)
         hook_state = None
         if comm in ("auto", "nvlink"):
@@ -251,6 +259,8 @@ def run_b200(args) -> dict:
             wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
         wrapped._b200sft_hook = True
     params = [p for p in model.parameters() if p.requires_grad]
+    if stock:
+        args.tail = "torch"
     if args.tail == "b200":
         from llm_fine_tune_distributed_b200.optim import B200AdamW
 
@@ -267,7 +277,11 @@ def run_b200(args) -> dict:
 
     bwd_done = [] if (world > 1 and isinstance(hook_state, B200NvlinkState)) else None
 
-    def opt_step(window_dev) -> torch.Tensor:
+    def stock_loss(mb, n_items) -> torch.Tensor:
+        """Trainer.compute_loss's default path (SP/transformers/trainer.py:1973-2019): the model's own loss."""
+        return wrapped(**mb, num_items_in_batch=n_items).loss * world
+
+    def opt_step(window_dev, use_stock: bool = stock) -> torch.Tensor:
         """One optimizer step on device-resident micro-batches; returns the summed loss."""
         n_items = sum(mb["labels"].ne(-100).sum() for mb in window_dev)  # Trainer._get_num_items_in_batch
         if world > 1:
@@ -277,14 +291,21 @@ def run_b200(args) -> dict:
             last = i == len(window_dev) - 1
             ctx = contextlib.nullcontext() if (last or world == 1) else wrapped.no_sync()
             with ctx:
-                loss = seam.compute_loss(wrapped, dict(mb), num_items_in_batch=n_items)
+                if use_stock:
+                    loss = stock_loss(dict(mb), n_items)
+                else:
+                    loss = seam.compute_loss(wrapped, dict(mb), num_items_in_batch=n_items)
                 loss.backward()
             if last and bwd_done is not None:   # backward() returns after DDP has waited for every bucket
                 ev = torch.cuda.Event(enable_timing=True)
                 ev.record()
                 bwd_done.append(ev)
             total_loss += loss.detach()
-        if args.tail == "b200":
+        if use_stock and not stock:         # the in-line stock_gpu block of this library's arm: torch's own tail
+            torch.nn.utils.clip_grad_norm_(params, 1.0)
+            stock_opt[0].step()
+            stock_opt[0].zero_grad(set_to_none=True)
+        elif args.tail == "b200":
             opt.clip_and_step(1.0)          # grad-norm + clip + AdamW in this library's multi-tensor kernels
         else:
             torch.nn.utils.clip_grad_norm_(params, 1.0)
@@ -292,10 +313,12 @@ def run_b200(args) -> dict:
         opt.zero_grad(set_to_none=True)
         return total_loss
 
+    stock_opt = [None]
+
     to_dev = lambda mb: {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) else v) for k, v in mb.items()}
     token_counts = {}
 
-    def timed(steps: int, e2e: bool, first_step: int):
+    def timed(steps: int, e2e: bool, first_step: int, use_stock: bool = stock):
         # every rank draws its own data (seed offset by rank), as a sharded sampler would hand it out
         windows = [synthetic_window((first_step + s) * 64 + rank, GA, B, T, pin=e2e, workload=args.workload)
                    for s in range(steps)]
@@ -313,7 +336,7 @@ def run_b200(args) -> dict:
         for w in windows:
             if e2e:
                 w = [to_dev(mb) for mb in w]                        # H2D of the step's inputs (pinned)
-            loss = opt_step(w)
+            loss = opt_step(w, use_stock)
             if e2e:
                 last_loss = loss.item()                             # D2H of the step's result
         ev1.record()
@@ -333,6 +356,7 @@ def run_b200(args) -> dict:
     if rank == 0 and not args.no_clocks:
         sampler.start()
     ops.STATS.reset(with_events=True)
+    torch.cuda.reset_peak_memory_stats(dev)
     if bwd_done is not None:
         hook_state.timeline = []
         bwd_done.clear()
@@ -358,6 +382,21 @@ def run_b200(args) -> dict:
     else:
         ms_e2e, wall_e2e, last_loss = timed(args.steps, e2e=True, first_step=200)
     clocks = sampler.stop() if rank == 0 else None
+    peak_mem_gb = torch.cuda.max_memory_allocated(dev) / 1e9
+    stock_gpu = None
+    if world == 1 and not stock and not args.no_stock_gpu:
+        # the same step on the stock GPU path (what training.py would run on this box without this library):
+        # same model object, weights, data and GA; transformers' lm_head + ForCausalLMLoss, torch's clip + fused AdamW
+        stock_opt[0] = torch.optim.AdamW(params, lr=5e-5 * world, weight_decay=0.0, fused=True)
+        torch.cuda.reset_peak_memory_stats(dev)
+        timed(1, e2e=False, first_step=300, use_stock=True)
+        ms_stock, _, _ = timed(3, e2e=False, first_step=301, use_stock=True)
+        stock_gpu = {"ms_per_step": round(ms_stock, 3),
+                     "value": round(token_counts[301][0] / 3 / (ms_stock / 1e3), 1), "unit": UNIT, "steps": 3, "warmup": 1,
+                     "max_memory_allocated_GB": round(torch.cuda.max_memory_allocated(dev) / 1e9, 2),
+                     "path": "stock transformers lm_head + ForCausalLMLoss (logits materialised), torch clip_grad_norm_ + "
+                             "fused AdamW; same model, data, GA; peak memory includes this arm's 1.7 GB of AdamW state"}
+        stock_opt[0] = None
 
     def all_ranks(x: float) -> float:
         t = torch.tensor([x], device=dev, dtype=torch.float64)
@@ -395,7 +434,7 @@ def run_b200(args) -> dict:
     N = B * T
     peaks = read_peaks()
     fwd_flops = 2.0 * N * H * V
-    achieved = fwd_flops / (fwd_ms / 1e3) / 1e12
+    achieved = fwd_flops / (fwd_ms / 1e3) / 1e12 if not stock else float("nan")
     traffic = tensor_pct = None
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
@@ -410,15 +449,17 @@ def run_b200(args) -> dict:
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {
             "workload": f"SmolLM3-3B random-init bf16 SFT optimizer step: seq {T}, per-device batch {B}, grad-accum {GA}, "
-                        "freeze policy last-2-layers+tied lm_head, gradient checkpointing, fused LM-head+CE (sm_100a), "
-                        f"clip 1.0 + AdamW ({args.tail} kernels)" + (f", DDP bucket 50 MiB + b200 comm hook ({args.comm})" if world > 1 else ""),
+                        "freeze policy last-2-layers+tied lm_head, gradient checkpointing, "
+                        + ("stock lm_head + ForCausalLMLoss (logits materialised), " if stock else "fused LM-head+CE (sm_100a), ")
+                        + f"clip 1.0 + AdamW ({args.tail} kernels)"
+                        + (f", DDP bucket 50 MiB + {'built-in allreduce' if stock else f'b200 comm hook ({args.comm})'}" if world > 1 else ""),
             "global_batch": B * GA * world, "seq_len": T, "parallelism": f"dp{world}", "attn": attn,
             "rows": {"full": "full-length rows, every position trains",
                      "padded": "variable-length rows right-padded to seq_len (reference collator), -100 on padding",
                      "packed": "variable-length samples packed to seq_len, flattened [1, B*T], restarting position_ids, "
                                "-100 at sample starts, FA2 varlen"}[args.workload],
             "tokens_per_step": round(tokens_per_step, 1), "valid_label_tokens_per_step": round(valid_dev / args.steps, 1),
-            "skip_ignored_rows": True, "final_norm": args.final_norm,
+            "skip_ignored_rows": not stock, "final_norm": "stock" if stock else args.final_norm,
             "layers": model.config.num_hidden_layers, "trainable_params": trainable, "total_params": total,
             "l2": "working set (6.2 GB of weights + activations per pass) far exceeds the 126 MB L2; no explicit flush",
             "attention_mask": "None (full-length rows; identical to an all-ones mask)",
@@ -445,7 +486,15 @@ def run_b200(args) -> dict:
                      "achieved_tflops": round(4.0 * N * H * V / (bwd_ms / 1e3) / 1e12, 1),
                      "frac_of_sustained_peak": round(4.0 * N * H * V / (bwd_ms / 1e3) / 1e12 / peaks["sustained"], 4)},
         "wall_s": {"device_timed": round(wall_dev, 3), "e2e_timed": round(wall_e2e, 3)},
+        "max_memory_allocated_GB": round(peak_mem_gb, 2),
     }
+    if stock_gpu is not None:
+        res["stock_gpu"] = stock_gpu
+    if stock:  # none of this library's kernels ran: no roofline of ours to report
+        res["impl"] = "stock"
+        for k in ("roofline", "flce_bwd"):
+            res.pop(k)
+        res["gpu_launches"] = 0
     if hook_state is not None:
         n_steps = args.steps * (1 if args.no_e2e else 2) + max(args.warmup, 3)
         res["comm"] = {"hook": args.comm, "path": getattr(hook_state, "path_used", "nccl"),
@@ -453,25 +502,37 @@ def run_b200(args) -> dict:
                        "bytes_reduced_per_step": round(hook_state.bytes_reduced / max(n_steps, 1))}
         if comm_times:
             res["comm"].update(comm_times)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        res["cpu_baseline"] = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=1)
     if world > 1:
-        dist.destroy_process_group()
+        dist.destroy_process_group()   # the other ranks leave; rank 0 alone times the CPU baseline on the free cores
+    if rank == 0 and not args.no_cpu_baseline and not stock:
+        del opt, wrapped, seam
+        torch.cuda.empty_cache()
+        res["cpu_baseline"] = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=1, warmup=1)
     return res if rank == 0 else {}
 
 
 # ------------------------------------------------------------------------------------------
 # reference arm / CPU baseline: the reference's own arithmetic on the host cores
 # ------------------------------------------------------------------------------------------
-def cpu_reference_step(sample_tokens: int, steps: int) -> dict:
-    """One optimizer step of the reference path on CPU: stock SmolLM3ForCausalLM forward with
-    labels (lm_head -> ForCausalLMLoss, i.e. oracle.lm_head_ce's arithmetic inside transformers),
-    autograd backward, clip, AdamW -- on a bounded sample of B=1 x ``sample_tokens`` tokens of the
-    same 3B architecture, all host threads."""
-    from oracle import sft_oracle as oracle  # noqa: F401  (the checker restates this path; see its header)
+def host_threads() -> int:
+    """Cores this process may run on.  torchrun exports OMP_NUM_THREADS=1 to every rank, which would leave the CPU
+    arm on one core at N > 1; the arm runs on rank 0 alone, so it takes every core of the affinity mask."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:  # not Linux
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_reference_step(sample_tokens: int, steps: int, warmup: int = 1, budget_s: float = 240.0) -> dict:
+    """Optimizer steps of the reference path on CPU: stock SmolLM3ForCausalLM forward with labels (lm_head ->
+    ForCausalLMLoss inside transformers), autograd backward, clip, AdamW (training.py:300's step) -- each on a
+    bounded sample of B=1 x ``sample_tokens`` tokens of the same 3B architecture, on all host threads.
+    ``warmup`` untimed steps of the same size (after one 16-token pass that spins up the thread pool), then up to
+    ``steps`` timed ones; stops early once ``budget_s`` seconds of timed work are spent (reported as steps_run)."""
     from llm_fine_tune_distributed_b200.training import apply_freeze_policy
 
-    threads = torch.get_num_threads()
+    threads = host_threads()
+    torch.set_num_threads(threads)
     t_build = time.perf_counter()
     if torch.cuda.is_available():  # initialise on the GPU (fast), then move: initialisation is not timed
         model = build_model(torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))), "sdpa").cpu()
@@ -485,7 +546,8 @@ def cpu_reference_step(sample_tokens: int, steps: int) -> dict:
     opt = torch.optim.AdamW(params, lr=5e-5)
     t_build = time.perf_counter() - t_build
     times = []
-    for s in range(steps + 1):  # first pass on 16 tokens only warms the thread pool / allocator
+    spent = 0.0
+    for s in range(1 + warmup + steps):
         T = 16 if s == 0 else sample_tokens
         ids = torch.randint(0, V, (1, T), generator=torch.Generator().manual_seed(99 + s))
         n_items = ids.ne(-100).sum()
@@ -495,29 +557,37 @@ def cpu_reference_step(sample_tokens: int, steps: int) -> dict:
         torch.nn.utils.clip_grad_norm_(params, 1.0)
         opt.step()
         opt.zero_grad(set_to_none=True)
+        dt = time.perf_counter() - t0
+        if s > warmup:
+            times.append(dt)
         if s > 0:
-            times.append(time.perf_counter() - t0)
+            spent += dt
+        if times and spent > budget_s:
+            break
     sec = sum(times) / len(times)
     return {"value": round(sample_tokens / sec, 2), "unit": UNIT, "cores": threads, "kind": "port",
-            "os_cpu_count": os.cpu_count(), "seconds_per_sample_step": round(sec, 3),
-            "sample": f"1 optimizer step on B=1 x T={sample_tokens} tokens of the same SmolLM3-3B workload "
+            "os_cpu_count": os.cpu_count(), "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
+            "torch_num_threads": torch.get_num_threads(), "seconds_per_sample_step": round(sec, 3),
+            "steps_run": len(times), "warmup_run": warmup,
+            "sample": f"{len(times)} optimizer step(s) on B=1 x T={sample_tokens} tokens of the same SmolLM3-3B workload "
                       "(stock transformers lm_head + ForCausalLMLoss + autograd + AdamW, sdpa attention, torch CPU "
                       f"kernels, {threads} threads); model build {t_build:.1f}s not timed"}
 
 
 def run_reference(args) -> dict:
+    """``--impl reference``: under torchrun rank 0 alone runs and prints; the other ranks exit 0 without work."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return {}
-    steps = max(1, min(args.steps, 3))
-    cb = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=steps)
+    cb = cpu_reference_step(sample_tokens=args.cpu_tokens, steps=max(1, args.steps), warmup=max(1, args.warmup))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     return {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world,
-        "steps": steps, "warmup": 1, "ms_per_step": round(cb["seconds_per_sample_step"] * 1e3, 1),
+        "steps": cb["steps_run"], "steps_requested": args.steps, "warmup": cb["warmup_run"],
+        "warmup_requested": args.warmup, "ms_per_step": round(cb["seconds_per_sample_step"] * 1e3, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": "SmolLM3-3B random-init bf16 SFT optimizer step, reference path on host CPU cores "
-                               f"(bounded sample B=1 x T={args.cpu_tokens}; rank 0 only)",
+                               f"(bounded sample B=1 x T={args.cpu_tokens} per step; rank 0 only, {cb['cores']} threads)",
                    "global_batch": 1, "seq_len": args.cpu_tokens, "parallelism": "cpu"},
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -530,7 +600,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "stock"],
+                    help="b200 = this repository; reference = the reference step on the host CPU cores; stock = the same "
+                         "step on the GPU through stock transformers / torch / DDP (what training.py runs without this library)")
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--seq", type=int, default=1024)
     ap.add_argument("--ga", type=int, default=2)
@@ -549,6 +621,7 @@ def main():
     ap.add_argument("--cpu-tokens", type=int, default=1024,
                     help="CPU baseline / reference arm: tokens in the bounded sample (one row of the workload by default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stock-gpu", action="store_true", help="skip the in-line stock-GPU-path block (N=1 only)")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer pass")
     ap.add_argument("--no-clocks", action="store_true", help="profiling runs only: do not spawn the nvidia-smi sampler")
     ap.add_argument("--kernel-table", default=None, metavar="PATH",

@@ -193,7 +193,9 @@ int b200sft_rmsnorm_scatter_bwd(const void* dyc, const void* h, const void* gamm
  * make that first call before starting any stream capture.  All calls on a device share the one
  * array, which still holds the previous call's contents: the call itself clears the part that
  * must start at zero, but two calls that overlap on the GPU (different streams, no dependency)
- * race on it -- serialise them.
+ * race on it -- serialise them.  The 40 MiB are reserved when the CUDA runtime loads the library's
+ * device image on that device, which happens at the latest during this first call: make it while
+ * that much HBM is still free, not after another allocator has taken the rest.
  */
 #define B200SFT_NOALLOC_SCRATCH_BYTES (40u << 20)
 int b200sft_flce_fwd_noalloc(const void* x, const void* w, const int32_t* labels, int N, int H, int V,
@@ -239,7 +241,11 @@ int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K
  * Gradient-bucket scale / cast kernels for the DDP communication hook.  Replace
  *   tensor.div_(world_size)                      SP/torch/distributed/algorithms/ddp_comm_hooks/default_hooks.py:18-32
  *   buffer.to(bf16).div_(world_size); copy back  .../default_hooks.py:57-93 (bf16_compress_hook)
- * (DDP is configured at training.py:249-256).  128-bit vectorised, grid-stride, HBM-bound.
+ * (DDP is configured at training.py:249-256).  128-bit vectorised, one contiguous run per block, HBM-bound.
+ * Pass scale = 1/world rounded to fp32: on CUDA, ATen's div_ by a host scalar is itself a multiply by
+ * that fp32 reciprocal (BinaryDivTrueKernel.cu: "a * reciprocal(b)"), so the result has the reference's
+ * bits for every world size, not only powers of two (tests: worlds 2..8 against tensor.div_ on the GPU).
+ * scale_cast rounds to bf16 first, scales in fp32 and rounds again, as buffer.to(bf16).div_(world) does.
  */
 int b200sft_scale_bf16_inplace(void* buf, size_t n, float scale, void* stream);
 int b200sft_scale_f32_inplace(float* buf, size_t n, float scale, void* stream);

@@ -243,6 +243,7 @@ label_frontend_kernel(LabelSources in, int B, int T, int64_t* __restrict__ label
 // ---------------------------------------------------------------------------------------------
 // scale / cast (gradient buckets)
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float round_bf16_f32(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 __device__ __forceinline__ uint32_t scale_bf16x2(uint32_t v, float s) {
   __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
   float2 f = __bfloat1622float2(h);
@@ -286,10 +287,15 @@ struct ScaleF32x4 {
   float s;
   __device__ __forceinline__ float4 operator()(float4 x) const { return make_float4(x.x * s, x.y * s, x.z * s, x.w * s); }
 };
+// bf16_compress_hook rounds to bf16 BEFORE it divides (default_hooks.py:74: buffer.to(bf16).div_(world)), so the
+// value is rounded, scaled in fp32 and rounded again -- identical to one rounding for power-of-two scales, and
+// the reference's bits for every other world size.
+__device__ __forceinline__ float compress_one(float a, float s) { return round_bf16_f32(a) * s; }
 struct F32x4ToBf16x4 {
   float s;
   __device__ __forceinline__ uint2 operator()(float4 a) const {
-    __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x * s, a.y * s), p1 = __floats2bfloat162_rn(a.z * s, a.w * s);
+    __nv_bfloat162 p0 = __floats2bfloat162_rn(compress_one(a.x, s), compress_one(a.y, s)),
+                   p1 = __floats2bfloat162_rn(compress_one(a.z, s), compress_one(a.w, s));
     return make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
   }
 };
@@ -351,7 +357,7 @@ __global__ void __launch_bounds__(EW_THREADS)
   if (vec_ok ? blockIdx.x == 0 : true) {
     const size_t stride = vec_ok ? blockDim.x : static_cast<size_t>(gridDim.x) * blockDim.x;
     const size_t first = vec_ok ? threadIdx.x : blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
-    for (size_t i = done + first; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i] * s);
+    for (size_t i = done + first; i < n; i += stride) dst[i] = __float2bfloat16_rn(compress_one(src[i], s));
   }
 }
 

@@ -302,9 +302,20 @@ class FusedCELossMixin:
         if average and num_items_in_batch is not None and getattr(self, "model_accepts_loss_kwargs", True):
             loss = loss * self._b200sft_num_processes()
         if return_outputs:
-            # the fused path never forms logits: hand back outputs with logits cleared so that a
-            # caller that expects them fails visibly instead of reading hidden states
-            if hasattr(outputs, "logits"):
-                outputs.logits = None
-            return loss, outputs
+            return loss, _without_logits(outputs)
         return loss
+
+
+def _without_logits(outputs: Any) -> Any:
+    """The fused path never forms logits; what sits under the ``logits`` key is the [B,T,H] hidden states the armed
+    head passed through.  Hand back outputs WITHOUT that key, so a caller that expects logits
+    (``Trainer.prediction_step`` builds them from ``outputs.items()``, SP/transformers/trainer.py:2953-2975;
+    ``compute_metrics``; ``preprocess_logits_for_metrics``) fails visibly instead of scoring hidden states.
+    Setting the attribute to None is not enough: ``ModelOutput.__setattr__`` leaves the dict entry in place."""
+    if isinstance(outputs, dict):  # ModelOutput is an OrderedDict subclass
+        kept = {k: v for k, v in outputs.items() if k != "logits"}
+        try:
+            return type(outputs)(**kept)
+        except TypeError:  # an output class whose constructor insists on logits: a plain dict carries the rest
+            return kept
+    return outputs

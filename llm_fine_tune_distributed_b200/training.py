@@ -33,12 +33,19 @@ from .loss import FusedCELossMixin
 
 MODEL_NAME = "HuggingFaceTB/SmolLM3-3B"  # training.py:54
 
-# training.py:176-186 -- data, not code: the system prompt every sample is formatted with
-SYSTEM_PROMPT = (
-    "You are a wilderness survival and practical skills expert. Your mission is to provide comprehensive, "
-    "detailed guidance on essential survival and practical skills. Give thorough, step-by-step instructions "
-    "with explanations of why each step matters."
-)
+# training.py:176-186 -- data, not code: the system prompt every sample is formatted with, in full (it is part of
+# every tokenised row, so a shortened prompt would change the row lengths and hence the padding mask)
+SYSTEM_PROMPT = """You are a wilderness survival and practical skills expert. Your mission is to provide comprehensive, detailed guidance on essential survival and practical skills. Give thorough, step-by-step instructions with explanations of why each step matters.
+
+Your expertise covers:
+- Wilderness Survival Basics: Rule of 3s (3 minutes without air, 3 hours without shelter in harsh conditions, 3 days without water, 3 weeks without food), emergency signaling techniques, essential knots, identifying poisonous plants and safe alternatives
+- Basic First Aid: Treatment for cuts, burns, sprains, shock, and emergency care procedures
+- Simple Car Maintenance: Checking fluids (oil, coolant, brake, transmission), tire inspection and pressure, lights and electrical systems
+- Basic Cooking Techniques: Food safety, preparation methods, cooking over open fires, food preservation
+- Common Measurement Conversions: Imperial to metric, cooking measurements, distance and weight conversions
+- Essential Knots: Bowline, clove hitch, trucker's hitch, figure-eight, sheet bend, and their practical applications
+
+Always provide detailed explanations, safety warnings when relevant, and multiple approaches when possible. Your responses should be comprehensive enough to help someone learn and apply these skills safely and effectively. Aim for thorough, educational responses rather than brief answers."""
 
 
 # --------------------------------------------------------------------------------------------
@@ -428,9 +435,11 @@ class MiniSFTTrainer(FusedCELossMixin):
     @torch.no_grad()
     def evaluate(self) -> Dict[str, float]:
         """``Trainer.evaluate`` for this configuration (eval_strategy="steps", eval_steps=10,
-        metric_for_best_model="eval_loss": training.py:270-275): the model loss of every validation
-        batch -- same fused path, no_grad, ``num_items_in_batch`` None so each batch is a mean over
-        its valid tokens -- averaged over batches and ranks."""
+        metric_for_best_model="eval_loss": training.py:270-275): the loss of every validation batch as
+        ``Trainer.prediction_step`` computes it (SP/transformers/trainer.py:2951-2957) -- same fused path, no_grad,
+        ``num_items_in_batch`` = the batch's UNSHIFTED non-ignored label count summed over ranks
+        (``_get_num_items_in_batch([inputs])``), handed to ``compute_loss``, which multiplies by the number of
+        processes -- averaged over batches and ranks."""
         if self.eval_batches is None or len(self.eval_batches) == 0:
             return {}
         was_training = self.model_wrapped.training
@@ -440,10 +449,17 @@ class MiniSFTTrainer(FusedCELossMixin):
         n = 0
         for inputs in self.eval_batches.epoch(0):
             inputs = self._on_device(inputs)
+            plan = inputs.get("b200sft_plan")
+            count = (plan.counts[0] if plan is not None else inputs["labels"].ne(-100).sum()).to(self.device).clone()
+            if self.args.average_tokens_across_devices and self.world > 1:
+                dist.all_reduce(count, op=dist.ReduceOp.SUM)
             if self.loss_impl is not None:
-                total += self.loss_impl(self.model, inputs, None).float()
-            else:
-                total += self.compute_loss(self.model, inputs).float()   # unwrapped model, as prediction_step uses it
+                loss = self.loss_impl(self.model, inputs, count).float()
+                if self.args.average_tokens_across_devices:
+                    loss = loss * self.num_processes
+                total += loss
+            else:  # unwrapped model, as prediction_step uses it
+                total += self.compute_loss(self.model, inputs, num_items_in_batch=count).float()
             n += 1
         if self.world > 1:
             dist.all_reduce(total, op=dist.ReduceOp.SUM)
@@ -528,9 +544,19 @@ def build_trainer(model: nn.Module, settings: SFTSettings, train_rows, val_rows,
         class FusedSFTTrainer(FusedCELossMixin, SFTTrainer):
             pass
 
-        cfg = SFTConfig(**{k: v for k, v in settings.__dict__.items() if k in SFTConfig.__dataclass_fields__})
-        return FusedSFTTrainer(model=model, args=cfg, train_dataset=[format_prompt(r) for r in train_rows],
-                               eval_dataset=[format_prompt(r) for r in val_rows], callbacks=list(callbacks))
+        from datasets import Dataset
+
+        fields = SFTConfig.__dataclass_fields__
+        kw = {k: v for k, v in settings.__dict__.items() if k in fields}
+        if "max_seq_length" not in fields and "max_length" in fields:  # TRL >= 0.20 renamed the field
+            kw["max_length"] = settings.max_seq_length
+        cfg = SFTConfig(**kw)
+        # [TRL, not on disk] untested in the build image (trl / accelerate are not installable there): INTEGRATION.md 1
+        return FusedSFTTrainer(model=model, args=cfg,
+                               train_dataset=Dataset.from_list([format_prompt(r) for r in train_rows]),
+                               eval_dataset=Dataset.from_list([format_prompt(r) for r in val_rows]),
+                               processing_class=tokenizer if hasattr(tokenizer, "save_pretrained") else None,
+                               callbacks=list(callbacks))
     except ImportError:
         pass
     completion_only = os.getenv("COMPLETION_ONLY", "0") == "1" and isinstance(tokenizer, ByteChatTokenizer)

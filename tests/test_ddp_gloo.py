@@ -36,7 +36,9 @@ def _hook_worker(rank, world, port, ret):
         ddp = DDP(net, bucket_cap_mb=1)
         state = None
         if use_hook:
-            state = B200HookState(None, scale_fn=lambda buf, s: buf.mul_(s))  # CPU stand-in for the scale kernel
+            # CPU stand-in for the scale kernel: the hook hands over 1/world; torch's CPU div_ is a true division
+            # (only its CUDA kernel multiplies by the reciprocal), so divide here to keep stock DDP's bits at world 3
+            state = B200HookState(None, scale_fn=lambda buf, s: buf.div_(round(1.0 / s)))
             ddp.register_comm_hook(state, b200_allreduce_hook)
         g = torch.Generator().manual_seed(10 + rank)
         x = torch.randn(16, 64, generator=g).to(torch.bfloat16)
@@ -51,14 +53,15 @@ def _hook_worker(rank, world, port, ret):
     same = all(torch.equal(a, b) for a, b in zip(stock, ours))
     gathered = [torch.zeros_like(ours[0]) for _ in range(world)]
     dist.all_gather(gathered, ours[0])
-    ret[rank] = (same, fired_early, fired, bool(torch.equal(gathered[0], gathered[1])))
+    ret[rank] = (same, fired_early, fired, all(bool(torch.equal(gathered[0], t)) for t in gathered[1:]))
     dist.destroy_process_group()
 
 
-def test_comm_hook_equals_stock_ddp_gloo_world2():
+@pytest.mark.parametrize("world", [2, 3])   # 3: a world that is not a power of two (1/world is not exact in bf16)
+def test_comm_hook_equals_stock_ddp_gloo(world):
     ret = mp.Manager().dict()
-    mp.spawn(_hook_worker, args=(2, 29621, ret), nprocs=2, join=True)
-    for r in range(2):
+    mp.spawn(_hook_worker, args=(world, 29621 + world, ret), nprocs=world, join=True)
+    for r in range(world):
         same, fired_early, fired, equal_across = ret[r]
         assert same, "grads differ from DDP's built-in allreduce"
         assert fired_early == 0 and fired >= 1

@@ -92,6 +92,41 @@ def test_largest_config_properties(cuda_device):
     assert torch.equal(dx2, dx1 * 2) and torch.equal(dw2, dw1 * 2)
 
 
+@pytest.mark.parametrize("skip", [False, True])
+def test_largest_config_against_row_blocked_oracle(cuda_device, skip):
+    """BASELINE config 4's largest point (65,536 tokens x 2048 x 128,256; 50 % of the labels masked) against the
+    oracle itself: cross-entropy is a sum over rows, so the oracle is evaluated 4,096 rows at a time
+    (oracle.lm_head_ce_with_grads_chunked, pinned on the golden fixtures by tests/test_oracle_golden.py) and never
+    holds more than a 2.1 GB block of logits.  Tolerances are BASELINE's: loss 1e-3 relative, gradient cosine
+    >= 0.999, max-rel-err (of the largest gradient magnitude) printed and bounded."""
+    from llm_fine_tune_distributed_b200 import ops
+
+    Nbig = 65536
+    x = torch.randn(Nbig, H, generator=torch.Generator().manual_seed(5)).to(torch.bfloat16).to(cuda_device)
+    w = (torch.randn(V, H, generator=torch.Generator().manual_seed(1)) * 0.02).to(torch.bfloat16).to(cuda_device)
+    labels = torch.randint(0, V, (Nbig,), generator=torch.Generator().manual_seed(6))
+    labels[torch.rand(Nbig, generator=torch.Generator().manual_seed(7)) < 0.5] = -100
+    labels = labels.to(cuda_device)
+    n_items = torch.tensor(int((labels != -100).sum()) + 5, dtype=torch.int64, device=cuda_device)
+    xg, wg = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    loss = ops.fused_linear_cross_entropy(xg, wg, labels.to(torch.int32), n_items, skip_ignored_rows=skip)
+    loss.backward()
+    dx, dw = xg.grad, wg.grad
+    del xg, wg
+    ref_loss, ref_dx, ref_dw = oracle.lm_head_ce_with_grads_chunked(x, w, labels, float(n_items), rows_per_chunk=4096)
+    torch.cuda.synchronize()
+    rel_loss = abs(loss.item() - ref_loss.item()) / abs(ref_loss.item())
+    cdx, cdw = _cos(dx, ref_dx), _cos(dw, ref_dw)
+    rel_dx = float((dx.float() - ref_dx.float()).abs().max() / ref_dx.float().abs().max())
+    rel_dw = float((dw.float() - ref_dw.float()).abs().max() / ref_dw.float().abs().max())
+    print(f"N=65536 (skip_ignored_rows={skip}): loss {loss.item():.6f} vs oracle {ref_loss.item():.6f} (rel {rel_loss:.2e}); "
+          f"cos dx {cdx:.6f} dw {cdw:.6f}; max-rel-err dx {rel_dx:.3e} dw {rel_dw:.3e}")
+    assert rel_loss <= 1e-3
+    assert cdx >= 0.999 and cdw >= 0.999
+    assert rel_dx <= 2e-2 and rel_dw <= 2e-2
+    assert torch.count_nonzero(dx[labels == -100]) == 0
+
+
 @pytest.mark.parametrize("Nn,Hh,Vv", [(1024, 4096, 151936), (768, 1024, 50264)])
 def test_other_model_shapes(cuda_device, Nn, Hh, Vv):
     """Not SmolLM3-specific: a wider hidden size and vocabularies that are not multiples of the 256-column

@@ -62,7 +62,10 @@ def test_compute_loss_seam_reproduces_trainer_compute_loss(tiny, monkeypatch):
         loss, outputs = seam.compute_loss(tiny, inputs, return_outputs=True, num_items_in_batch=n)
         ref = float(d[f"compute_loss_{i}"])
         assert abs(float(loss) - ref) <= 1e-6 * abs(ref)
-        assert outputs.logits is None
+        # no logits anywhere in what a caller can read: prediction_step builds its `logits` from outputs.items()
+        assert "logits" not in outputs.keys() and outputs.logits is None
+        assert all(v is not None and tuple(v.shape) != tuple(inputs["input_ids"].shape) + (tiny.config.hidden_size,)
+                   for v in outputs.to_tuple() if torch.is_tensor(v))
     # num_items_in_batch=None -> reduction="mean", no x num_processes (trainer.py:2013-2019)
     inputs = {"input_ids": torch.from_numpy(d["input_ids_0"]), "labels": torch.from_numpy(d["labels_0"])}
     loss = seam.compute_loss(tiny, inputs)

@@ -100,3 +100,20 @@ def test_rms_norm_restatement_is_the_transformers_module():
     ya.backward(g)
     yb.backward(g)
     assert torch.equal(a.grad, b.grad) and torch.equal(mod.weight.grad, w.grad)
+
+
+def test_chunked_restatement_equals_the_literal_path():
+    """The row-blocked form used at sizes where [N,V] fp32 logits do not fit (N = 65,536) against the golden
+    outputs of the real ForCausalLMLoss: loss to fp32 round-off, dX bit for bit when a block boundary falls
+    inside the batch (rows are independent), dW to one bf16 rounding (fp32 sum across blocks, other order)."""
+    d = np.load(os.path.join(G, "causal_lm_loss.npz"))
+    hidden, weight = _bf16(d["hidden"]), _bf16(d["weight"])
+    B, T, H = hidden.shape
+    shifted = oracle.shift_labels(torch.from_numpy(d["labels"])).reshape(-1)
+    n = float(d["num_items_sum"])
+    ref_dw = torch.from_numpy(d["dweight_sum"])
+    for rows in (B * T, 7, 1):
+        loss, dh, dw = oracle.lm_head_ce_with_grads_chunked(hidden.reshape(B * T, H), weight, shifted, n, rows_per_chunk=rows)
+        assert abs(float(loss) - float(d["loss_sum"])) <= 1e-6 * abs(float(d["loss_sum"]))
+        assert torch.equal(dh.float().reshape(B, T, H), torch.from_numpy(d["dhidden_sum"]))
+        assert float((dw.float() - ref_dw).abs().max()) <= 2.0 ** -8 * float(ref_dw.abs().max())

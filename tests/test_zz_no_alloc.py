@@ -5,8 +5,8 @@ ctypes/cgo-style stub that only ever sees tensors owned by another framework, a 
 when PyTorch's allocator has already claimed almost all of HBM (a raw cudaMalloc would fail), or
 code on the step's critical path where cudaMalloc/cudaFree would synchronise the device.  The
 variant keeps its scratch in a fixed 40 MiB array inside the library, so these tests drive it
-through ctypes exactly as such a caller would and compare it with the regular entry point (same
-kernels, caller-provided scratch) on two calls in a row: the second call reuses the array with the
+through ctypes exactly as such a caller would and compare it -- bit for bit -- with the regular entry
+point (same kernels, caller-provided scratch), and with the oracle, on two calls in a row: the second call reuses the array with the
 first call's leftovers in it, with a different shape and different labels.
 
 This file sorts last on purpose, so a run that stops at the first failure has already run
@@ -15,6 +15,8 @@ one-time address lookup).
 """
 import pytest
 import torch
+
+from oracle import sft_oracle as oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -64,10 +66,33 @@ def test_noalloc_forward_matches_regular_entry_point_twice(cuda_device):
             denom = torch.tensor(max(int((labels != -100).sum()), 1), dtype=torch.int64, device=cuda_device)
             ref_loss, ref_lse, ref_nv = _run(lib, False, x, w, labels, denom)
             loss, lse, nv = _run(lib, True, x, w, labels, denom)
-            # same tolerances as tests/test_gpu_flce.py: loss 1e-3 relative, lse 1e-3 absolute, count exact
-            assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
-            assert torch.allclose(lse, ref_lse, atol=1e-3, rtol=0)
-            assert int(nv) == int(ref_nv) == int((labels != -100).sum())
+            # Both entry points run the same deterministic kernels and differ only in where the scratch lives,
+            # so the outputs must agree exactly -- anything less would mean leftovers in the shared array leaked in.
+            assert torch.equal(loss, ref_loss) and torch.equal(lse, ref_lse) and torch.equal(nv, ref_nv)
+            assert int(nv) == int((labels != -100).sum())
+            # ... and against the oracle (the reference's lm_head + cross-entropy), with the tolerances of
+            # tests/test_gpu_flce.py: loss 1e-3 relative, lse 1e-3 absolute
+            want = oracle.lm_head_ce(x, w, labels.long(), float(denom))
+            assert abs(loss.item() - want.item()) <= 1e-3 * abs(want.item())
+            want_lse = torch.logsumexp(torch.nn.functional.linear(x, w).float(), dim=-1)
+            assert torch.allclose(lse, want_lse, atol=1e-3, rtol=0)
+
+
+def test_noalloc_on_a_second_device():
+    """The scratch array exists once per GPU and its address is looked up per device: the first call on device 1
+    must resolve device 1's copy, not reuse device 0's pointer."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from llm_fine_tune_distributed_b200 import _cabi
+
+    lib = _cabi.load()
+    for dev in (torch.device("cuda:0"), torch.device("cuda:1")):
+        with torch.cuda.device(dev):
+            x, w, labels = _inputs(512, 128, 4096, 0.4, 3, dev)
+            denom = torch.tensor(max(int((labels != -100).sum()), 1), dtype=torch.int64, device=dev)
+            ref = _run(lib, False, x, w, labels, denom)
+            got = _run(lib, True, x, w, labels, denom)
+            assert all(torch.equal(a, b) for a, b in zip(got, ref))
 
 
 def test_noalloc_rejects_oversized_request(cuda_device):

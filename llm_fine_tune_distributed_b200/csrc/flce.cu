@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/b200sft.h"
 #include "capi_common.h"
@@ -460,10 +461,10 @@ __global__ void scatter_rows_kernel(const __nv_bfloat16* __restrict__ dxc, const
 // same inputs the GEMM kernel used (live rows -> tiles -> choose_k_splits), so nothing is read back.
 __global__ void dx_combine_splits_kernel(const float* __restrict__ acc, size_t split_stride, int rows_cap, int H,
                                          const int* __restrict__ n_rows_dev, int tile_rows, int tiles_n, int workers,
-                                         int max_splits, __nv_bfloat16* __restrict__ out) {
+                                         int max_splits, int min_splits, __nv_bfloat16* __restrict__ out) {
   const int rows = n_rows_dev ? min(max(*n_rows_dev, 0), rows_cap) : rows_cap;
   const int tiles = ((rows + tile_rows - 1) / tile_rows) * tiles_n;
-  const int splits = choose_k_splits(tiles, workers, max_splits);
+  const int splits = choose_k_splits(tiles, workers, max_splits, min_splits);
   const size_t nvec = static_cast<size_t>(rows) * H / 4;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < nvec;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -566,10 +567,18 @@ int gemm_workers(int M, int N, int bn = BLOCK_N) {
   return static_cast<int>(tiles < max_w ? tiles : max_w);
 }
 
+// Per-launch options of the engine beyond the problem shape (see GemmShape for what each field does).
+struct GemmOpts {
+  const int* dyn_rows = nullptr;
+  int dyn_is_k = 0;
+  int max_k_splits = 1, min_k_splits = 1;
+  int ks_major = 0;
+  uint64_t a_l2_policy = 0, b_l2_policy = 0;
+};
+
 template <class Epi, bool A_MN, bool B_MN, int BN = 256>
 int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, int K, int m_fastest,
-                const typename Epi::Params& ep, cudaStream_t stream, const int* dyn_rows = nullptr, int dyn_is_k = 0,
-                int max_k_splits = 1) {
+                const typename Epi::Params& ep, cudaStream_t stream, const GemmOpts& o = GemmOpts()) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B200SFT_ERR_INVALID, "empty GEMM %dx%dx%d", M, N, K);
   const bool paired = (g_cta_group == 2);
   const int bn = paired ? BN : BLOCK_N;  // the single-CTA engine has one tile shape
@@ -588,9 +597,13 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.m_fastest = m_fastest;
   const int group = GROUP_M_ROWS / tile_m;
   s.group_m = s.tiles_m < group ? s.tiles_m : group;
-  s.dyn_rows = dyn_rows;
-  s.dyn_is_k = dyn_is_k;
-  s.max_k_splits = max_k_splits;
+  s.dyn_rows = o.dyn_rows;
+  s.dyn_is_k = o.dyn_is_k;
+  s.max_k_splits = o.max_k_splits;
+  s.min_k_splits = o.min_k_splits;
+  s.ks_major = o.ks_major;
+  s.a_l2_policy = o.a_l2_policy;
+  s.b_l2_policy = o.b_l2_policy;
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
   if (!paired) {
     auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
@@ -670,6 +683,25 @@ using namespace b200;
 
 namespace {
 
+// Tuning switches, read from the environment at each call (measurement aid; the defaults are what ships):
+//   B200SFT_L2_HINTS=0      TMA loads without eviction-priority hints
+//   B200SFT_DX_KS_MAJOR=0   dX work units tile-major (the round-1 order) instead of K-split-major
+//   B200SFT_DX_MIN_SPLITS=n force at least n K-splits of the dX GEMM (power of two); B200SFT_DX_MAX_SPLITS=n the cap (4)
+int tune_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v != nullptr && *v != 0) ? atoi(v) : dflt;
+}
+bool l2_hints_on() { return tune_int("B200SFT_L2_HINTS", 1) != 0; }
+
+// Logit GEMMs (forward, dlogits recompute): X is swept by every vocabulary panel of a rasterisation group, so it is
+// the operand to keep in the L2; W panels are read once per group.
+GemmOpts logit_gemm_opts(const int32_t* n_rows_dev) {
+  GemmOpts o;
+  o.dyn_rows = n_rows_dev;
+  if (l2_hints_on()) o.a_l2_policy = L2_EVICT_LAST;
+  return o;
+}
+
 struct FwdScratch {
   float2* partials;
   float* partials_ez;
@@ -737,11 +769,13 @@ int flce_fwd_impl(const void* x, const void* w, const int32_t* labels, int N, in
   if (stats) {
     FwdSoftmaxEpi<true>::Params ep = {labels, f.partials, f.partials_ez, f.tgt, N,
                                       (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0};
-    rc = launch_gemm<FwdSoftmaxEpi<true>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream, n_rows_dev, 0);
+    rc = launch_gemm<FwdSoftmaxEpi<true>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream,
+                                                        logit_gemm_opts(n_rows_dev));
   } else {
     FwdSoftmaxEpi<false>::Params ep = {labels, f.partials, nullptr, f.tgt, N,
                                        (flags & B200SFT_FLAG_ROUND_LOGITS_BF16) ? 1 : 0};
-    rc = launch_gemm<FwdSoftmaxEpi<false>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream, n_rows_dev, 0);
+    rc = launch_gemm<FwdSoftmaxEpi<false>, false, false>(x, H, w, H, N, V, H, /*m_fastest=*/1, ep, stream,
+                                                         logit_gemm_opts(n_rows_dev));
   }
   if (rc != 0) return rc;
 
@@ -763,7 +797,21 @@ int dx_max_k_splits(int N, int H) {
   const int workers = gemm_workers(N, H, DX_TILE_N);
   const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
   const long long tiles = static_cast<long long>((N + tile_m - 1) / tile_m) * ((H + DX_TILE_N - 1) / DX_TILE_N);
-  return tiles >= 16LL * workers ? 1 : 4;
+  return tiles >= 16LL * workers ? 1 : tune_int("B200SFT_DX_MAX_SPLITS", 4);
+}
+
+// With split-major order the tiles in flight share one K range of W[slab] (slab_cols / splits vocabulary rows of
+// H bf16 each); at least this many splits keep that range within DX_W_RANGE_L2_BYTES so it survives in the L2
+// from one wave of M tiles to the next.  Never more than dx_max_k_splits (each split owns an fp32 [N,H] buffer).
+constexpr size_t DX_W_RANGE_L2_BYTES = size_t(72) << 20;
+int dx_min_k_splits(int N, int H, int slab_cols) {
+  const int maxs = dx_max_k_splits(N, H);
+  const int forced = tune_int("B200SFT_DX_MIN_SPLITS", 0);
+  if (forced > 0) return forced < maxs ? forced : maxs;
+  if (tune_int("B200SFT_DX_KS_MAJOR", 1) == 0) return 1;
+  int s = 1;
+  while (s < maxs && static_cast<size_t>(slab_cols) * H * 2 / s > DX_W_RANGE_L2_BYTES) s *= 2;
+  return s;
 }
 
 }  // namespace
@@ -883,6 +931,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
   const int slab = resolve_slab_cols(N, V, chunk_cols);
   const int num_slabs = (V + slab - 1) / slab;
   const int dx_splits = dx_max_k_splits(N, H);
+  const int dx_min_splits = dx_min_k_splits(N, H, slab);
   const size_t dx_split_stride = align_up(static_cast<size_t>(N) * H * sizeof(float), 1024) / sizeof(float);
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   __nv_bfloat16* dlog = reinterpret_cast<__nv_bfloat16*>(ws);
@@ -909,7 +958,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = make_store_tmap(&dp.out_map, dlog, N, cols, slab);
     if (rc != 0) return rc;
     dp.col_offset = v0;
-    rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream, n_rows_dev, 0);
+    rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream,
+                                               logit_gemm_opts(n_rows_dev));
     if (rc != 0) return rc;
 
     // (2) dX[N,H] (+)= dlogits[N,cols] . W[v0:v0+cols, :]     A K-major, B = W rows read MN-major
@@ -930,8 +980,13 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
       sx.mode = ACCUM_F32_OUT_BF16;
     else
       sx.mode = ACCUM_F32;
-    rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream,
-                                                       n_rows_dev, 0, dx_splits);
+    GemmOpts ox;  // dlogits is streamed once per K range; the W rows of that range are what every tile re-reads
+    ox.dyn_rows = n_rows_dev;
+    ox.max_k_splits = dx_splits;
+    ox.min_k_splits = dx_min_splits;
+    ox.ks_major = tune_int("B200SFT_DX_KS_MAJOR", 1);
+    if (l2_hints_on()) ox.a_l2_policy = L2_EVICT_FIRST, ox.b_l2_policy = L2_EVICT_LAST;
+    rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream, ox);
     if (rc != 0) return rc;
     }
 
@@ -945,7 +1000,11 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     sw.split_stride = 0;
     sw.ld = H;
     sw.mode = STORE_BF16;
-    rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, n_rows_dev, 1);
+    GemmOpts ow;  // every wave of vocabulary tiles contracts over all of X: keep X, let dlogits stream past it
+    ow.dyn_rows = n_rows_dev;
+    ow.dyn_is_k = 1;
+    if (l2_hints_on()) ow.a_l2_policy = L2_EVICT_FIRST, ow.b_l2_policy = L2_EVICT_LAST;
+    rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, ow);
     if (rc != 0) return rc;
   }
   if (dx_splits > 1 && dx != nullptr) {
@@ -955,7 +1014,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     if (blocks > static_cast<size_t>(num_sms()) * 8) blocks = static_cast<size_t>(num_sms()) * 8;
     dx_combine_splits_kernel<<<static_cast<unsigned int>(blocks), 256, 0, stream>>>(
         dx_acc, dx_split_stride, N, H, n_rows_dev, tile_m, (H + DX_TILE_N - 1) / DX_TILE_N,
-        gemm_workers(N, H, DX_TILE_N), dx_splits, static_cast<__nv_bfloat16*>(dx));
+        gemm_workers(N, H, DX_TILE_N), dx_splits, dx_min_splits, static_cast<__nv_bfloat16*>(dx));
     B200_CUDA_CHECK(cudaGetLastError());
   }
   return B200SFT_OK;

@@ -55,6 +55,14 @@ struct GemmShape {
   // become separate work units.  Every piece accumulates into its own fp32 buffer (TileCoord::ks selects
   // it in the epilogue), so the result stays deterministic; the caller sums the buffers afterwards.
   int max_k_splits;
+  int min_k_splits;
+  // Work-unit order when the GEMM is K-split: 0 = unit -> (tile, split) with the split fastest; 1 = split-major,
+  // unit -> (split, tile): every tile of the GEMM is visited for one K range before the next range starts, so
+  // the tiles in flight at any time all read the SAME K range of both operands (dX: the same rows of W[slab],
+  // which then stay L2-resident across waves instead of being re-streamed for every wave of M tiles).
+  int ks_major;
+  // L2 eviction priority of the TMA loads of each operand (L2_EVICT_* in sm100_ptx.cuh; 0 = normal).
+  uint64_t a_l2_policy, b_l2_policy;
 };
 
 struct TileCoord {
@@ -62,10 +70,11 @@ struct TileCoord {
   int ks;  // K-split index of this work unit (0 when the GEMM is not split)
 };
 
-// Smallest power of two <= max_splits for which `tiles * splits` work units fill `workers` to >= 95 %
-// in whole rounds.  A pure function of its arguments: kernels, the host and the combine kernel agree.
-__host__ __device__ inline int choose_k_splits(int tiles, int workers, int max_splits) {
-  int s = 1;
+// Smallest power of two in [min_splits, max_splits] for which `tiles * splits` work units fill `workers` to
+// >= 95 % in whole rounds.  A pure function of its arguments: kernels, the host and the combine kernel agree.
+// min_splits > 1 is used with split-major order to keep one K range of the re-read operand L2-sized.
+__host__ __device__ inline int choose_k_splits(int tiles, int workers, int max_splits, int min_splits = 1) {
+  int s = min_splits > 1 ? min_splits : 1;
   while (s < max_splits) {
     const long long units = static_cast<long long>(tiles) * s;
     const long long rounds = (units + workers - 1) / workers;
@@ -79,10 +88,15 @@ __host__ __device__ inline int choose_k_splits(int tiles, int workers, int max_s
 struct UnitRange {
   int tile, ks, kb0, kb1;
 };
-__device__ __forceinline__ UnitRange unit_range(int unit, int splits, int num_kb) {
+__device__ __forceinline__ UnitRange unit_range(int unit, int splits, int num_kb, int num_tiles, int ks_major) {
   UnitRange u;
-  u.tile = unit / splits;
-  u.ks = unit - u.tile * splits;
+  if (ks_major) {
+    u.ks = unit / num_tiles;
+    u.tile = unit - u.ks * num_tiles;
+  } else {
+    u.tile = unit / splits;
+    u.ks = unit - u.tile * splits;
+  }
   const int per = (num_kb + splits - 1) / splits;
   u.kb0 = u.ks * per;
   u.kb1 = u.kb0 + per < num_kb ? u.kb0 + per : num_kb;
@@ -152,7 +166,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
-  const int splits = choose_k_splits(num_tiles, gridDim.x, shape.max_k_splits > 0 ? shape.max_k_splits : 1);
+  const int splits = choose_k_splits(num_tiles, gridDim.x, shape.max_k_splits > 0 ? shape.max_k_splits : 1, shape.min_k_splits);
   const int num_units = num_tiles * splits;
 
   if (warp == 0 && lane == 0) {
@@ -177,10 +191,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
     if (lane == 0) {
+      const uint64_t pol_a = shape.a_l2_policy ? shape.a_l2_policy : L2_EVICT_NORMAL;
+      const uint64_t pol_b = shape.b_l2_policy ? shape.b_l2_policy : L2_EVICT_NORMAL;
       int stage = 0;
       uint32_t phase = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
         const TileCoord tc = tile_coord(shape, ur.tile);
         for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -189,18 +205,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
           uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
           const int k0 = kb * BLOCK_K;
           if constexpr (!A_MN) {
-            tma_load_2d(&tmap_a, &full_bar[stage], sa, k0, tc.m0);  // box {64 k, 128 rows}
+            tma_load_2d(&tmap_a, &full_bar[stage], sa, k0, tc.m0, pol_a);  // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int j = 0; j < BLOCK_M / 64; ++j)  // box {64 m, 64 k-rows} per 64-wide M block
-              tma_load_2d(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0);
+              tma_load_2d(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0, pol_a);
           }
           if constexpr (!B_MN) {
-            tma_load_2d(&tmap_b, &full_bar[stage], sb, k0, tc.n0);  // box {64 k, 256 rows}
+            tma_load_2d(&tmap_b, &full_bar[stage], sb, k0, tc.n0, pol_b);  // box {64 k, 256 rows}
           } else {
 #pragma unroll
             for (int j = 0; j < BLOCK_N / 64; ++j)
-              tma_load_2d(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), tc.n0 + j * 64, k0);
+              tma_load_2d(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), tc.n0 + j * 64, k0, pol_b);
           }
           if (++stage == NUM_STAGES) {
             stage = 0;
@@ -223,7 +239,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       uint32_t phase = 0;
       int it = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
-        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
@@ -257,7 +273,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
-      const UnitRange ur = unit_range(unit, splits, num_kb);
+      const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
       TileCoord tc = tile_coord(shape, ur.tile);
       tc.ks = ur.ks;
       const int as = it & 1;
@@ -386,7 +402,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int num_pairs = gridDim.x >> 1;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
-  const int splits = choose_k_splits(num_tiles, num_pairs, shape.max_k_splits > 0 ? shape.max_k_splits : 1);
+  const int splits = choose_k_splits(num_tiles, num_pairs, shape.max_k_splits > 0 ? shape.max_k_splits : 1, shape.min_k_splits);
   const int num_units = num_tiles * splits;
 
   if (warp == 0 && lane == 0) {
@@ -411,10 +427,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   if (warp == 0) {
     // ------------------------------- TMA producer (both CTAs) -------------------------------
     if (lane == 0) {
+      const uint64_t pol_a = shape.a_l2_policy ? shape.a_l2_policy : L2_EVICT_NORMAL;
+      const uint64_t pol_b = shape.b_l2_policy ? shape.b_l2_policy : L2_EVICT_NORMAL;
       int stage = 0;
       uint32_t phase = 0;
       for (int unit = pair_id; unit < num_units; unit += num_pairs) {
-        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
         const TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
         const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
         for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
@@ -424,18 +442,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
           uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BLOCK_K;
           if constexpr (!A_MN) {
-            tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, tc.m0);  // box {64 k, 128 rows}
+            tma_load_2d_pair(&tmap_a, &full_bar[stage], sa, k0, tc.m0, pol_a);  // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int j = 0; j < BLOCK_M / 64; ++j)
-              tma_load_2d_pair(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0);
+              tma_load_2d_pair(&tmap_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), tc.m0 + j * 64, k0, pol_a);
           }
           if constexpr (!B_MN) {
-            tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, b_row0);  // box {64 k, 128 rows}
+            tma_load_2d_pair(&tmap_b, &full_bar[stage], sb, k0, b_row0, pol_b);  // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int j = 0; j < B_ROWS_PER_CTA / 64; ++j)
-              tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), b_row0 + j * 64, k0);
+              tma_load_2d_pair(&tmap_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), b_row0 + j * 64, k0, pol_b);
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -455,7 +473,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       uint32_t phase = 0;
       int it = 0;
       for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
-        const UnitRange ur = unit_range(unit, splits, num_kb);
+        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
@@ -489,7 +507,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
-      const UnitRange ur = unit_range(unit, splits, num_kb);
+      const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
       TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
       tc.ks = ur.ks;
       const int as = it & 1;

@@ -104,13 +104,20 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
 
+// L2 eviction-priority policies for TMA loads (the encodings createpolicy.fractional.L2::evict_* produces for
+// fraction 1.0).  An operand that every tile of a wave re-reads (X, a W panel range) is loaded evict_last so the
+// operand that is only streamed past it (the dlogits slab, loaded evict_first) cannot push it out of the L2.
+constexpr uint64_t L2_EVICT_NORMAL = 0x1000000000000000ull;
+constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull;
+constexpr uint64_t L2_EVICT_LAST = 0x14F0000000000000ull;
+
 // 2-D tile load global -> shared (this CTA), completion bytes on `bar` (this CTA).
 __device__ __forceinline__ void tma_load_2d(const CUtensorMap* m, uint64_t* bar, void* dst, int32_t c0,
-                                            int32_t c1) {
+                                            int32_t c1, uint64_t l2_policy = L2_EVICT_NORMAL) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
-          "r"(smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, "
+      "%4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(l2_policy)
       : "memory");
 }
 
@@ -118,12 +125,12 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* m, uint64_t* bar,
 // barrier at this offset in the *leader* CTA (rank 0 of the pair): clearing bit 24 of a
 // shared::cluster address selects the even CTA of the pair.
 __device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* m, uint64_t* bar, void* dst, int32_t c0,
-                                                 int32_t c1) {
+                                                 int32_t c1, uint64_t l2_policy = L2_EVICT_NORMAL) {
   uint32_t bar_leader = smem_u32(bar) & 0xFEFFFFFFu;
   asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
-      "%4}], [%2];" ::"r"(smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_leader), "r"(c0), "r"(c1)
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], "
+      "[%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_leader), "r"(c0), "r"(c1), "l"(l2_policy)
       : "memory");
 }
 

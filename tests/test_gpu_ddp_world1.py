@@ -96,9 +96,10 @@ def test_hooks_under_world1_nccl_ddp_match_stock(cuda_device):
     assert r["default_hook_equal"], "torch's own allreduce_hook differs from hook-less DDP (test setup broken)"
     assert r["bf16_equal"], "b200_allreduce_hook: gradients differ from stock DDP"
     assert r["compress_equal"], "b200_bf16_compress_hook: gradients differ from torch's bf16_compress_hook"
-    assert r["fired_under_no_sync"] == 0 and r["buckets"] >= 6       # >= 2 buckets x 3 synchronising backwards
+    print("buckets seen by the NCCL hook:", r["buckets"], "| NVLink hook at world 1:", r["nvlink"], r.get("nvlink_path"))
+    # one bucket in DDP's first iteration, the rebuilt (gradient-ready order, 2 MiB) buckets afterwards
+    assert r["fired_under_no_sync"] == 0 and r["buckets"] >= 4
     assert r["scale_launches"] >= r["buckets"]                       # the CUDA scale kernel ran for every bucket
-    print("NVLink hook at world 1:", r["nvlink"], r.get("nvlink_path"))
     if r["nvlink"] == "ran":
         assert r["nvlink_equal"], "b200_nvlink_allreduce_hook: gradients differ from stock DDP"
-        assert r["nvlink_early"] == 0 and r["nvlink_buckets"] >= 6 and r["nvlink_aligned"]
+        assert r["nvlink_early"] == 0 and r["nvlink_buckets"] >= 4 and r["nvlink_aligned"]

@@ -359,6 +359,7 @@ def run_b200(args) -> dict:
     torch.cuda.reset_peak_memory_stats(dev)
     if bwd_done is not None:
         hook_state.timeline = []
+        hook_state.phases = []
         bwd_done.clear()
     ms_step, wall_dev, _ = timed(args.steps, e2e=False, first_step=100)
     comm_times = None
@@ -369,10 +370,39 @@ def run_b200(args) -> dict:
         exposed = [tl[(i + 1) * per - 1][0].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
         busy = [sum(a.elapsed_time(b) for a, b, _ in tl[i * per:(i + 1) * per]) for i in range(len(bwd_done))]
         big = max(tl, key=lambda t: t[2])
+        ph = hook_state.phases
+        names = ("queue_ms", "copy_in_ms", "wait_for_peers_ms", "kernel_ms", "barrier_after_ms")
+
+        def phase_ms(rows):
+            return {nm: round(sum(r[i].elapsed_time(r[i + 1]) for r in rows) / max(len(bwd_done), 1), 3)
+                    for i, nm in enumerate(names)}
+
+        last_rows = [ph[(i + 1) * per - 1] for i in range(len(bwd_done))] if len(ph) == len(tl) else []
+        breakdown = None
+        if last_rows:
+            # the same phases on every rank, max and min over ranks: a large max-min of wait_for_peers is rank skew
+            # (the early ranks wait for the late ones), not transfer
+            mine = phase_ms(last_rows)
+            vec = torch.tensor([mine[nm] for nm in names], device=dev, dtype=torch.float64)
+            hi, lo = vec.clone(), vec.clone()
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            after = [last_rows[i][5].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
+            breakdown = {"last_bucket_rank0": mine, "last_bucket_max_over_ranks": dict(zip(names, [round(v, 3) for v in hi.tolist()])),
+                         "last_bucket_min_over_ranks": dict(zip(names, [round(v, 3) for v in lo.tolist()])),
+                         "copy_back_and_finalize_ms": round(sum(after) / len(after), 3),
+                         "all_buckets_rank0": phase_ms(ph),
+                         "note": "per optimizer step; phases of the hook on the side stream: queue = bucket ready -> side stream "
+                                 "free; copy_in = staging into the symmetric arena; wait_for_peers = first barrier; kernel = "
+                                 "reduce+scale+broadcast; barrier_after = second barrier; copy_back_and_finalize = last bucket "
+                                 "done -> backward() returns (DDP copies 838 MB of results into .grad)"}
+        hook_state.phases = []
         comm_times = {"exposed_ms_per_step": round(sum(exposed) / len(exposed), 3),
                       "hook_busy_ms_per_step": round(sum(busy) / len(busy), 3),
                       "largest_bucket": {"MiB": round(big[2] / 2**20, 1), "ms": round(big[0].elapsed_time(big[1]), 3),
                                          "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1)}}
+        if breakdown:
+            comm_times["breakdown"] = breakdown
         hook_state.timeline = None
     launches = ops.STATS.kernel_launches
     fwd_ms, bwd_ms = ops.STATS.mean_ms("flce_fwd"), ops.STATS.mean_ms("flce_bwd")

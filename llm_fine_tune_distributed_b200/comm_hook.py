@@ -159,6 +159,8 @@ class B200NvlinkState(B200HookState):
         self._offset = 0
         self._seen = set()
         self.trace = None  # set to a list to record (bucket index, numel, offset) per hook call (debugging)
+        # with `timeline` on: per hook call (ready, side-stream-free, staged, peers-arrived, kernel-done, done, bytes)
+        self.phases = []
 
     @classmethod
     def for_model(cls, model: torch.nn.Module, process_group: Optional[dist.ProcessGroup] = None, **kw):
@@ -224,9 +226,20 @@ def b200_nvlink_allreduce_hook(state: B200NvlinkState, bucket: dist.GradBucket) 
     side = state.side_stream(buf.device)
     side.wait_stream(cur)
     buf.record_stream(side)
+    marks = [] if ready is not None else None       # measurement aid: events between the phases, on the side stream
+
+    def mark():
+        if marks is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(side)
+            marks.append(ev)
+
     with torch.cuda.device(buf.device), torch.cuda.stream(side):
+        mark()                                      # side stream free (earlier buckets done) and the bucket is ready
         view.copy_(buf)
+        mark()                                      # staged in the arena
         hdl.barrier(channel=0)                      # every rank's copy is in place
+        mark()                                      # ... = how long this rank waited for its peers
         if state.use_multimem:
             _cabi.check(lib.b200sft_allreduce_scale_bf16_multimem(int(hdl.multicast_ptr) + 2 * off, padded, rank, world,
                                                                   1.0 / world, side.cuda_stream),
@@ -236,8 +249,11 @@ def b200_nvlink_allreduce_hook(state: B200NvlinkState, bucket: dist.GradBucket) 
             _cabi.check(lib.b200sft_allreduce_scale_bf16_p2p(ptrs, padded, rank, world, 1.0 / world, side.cuda_stream),
                         "b200sft_allreduce_scale_bf16_p2p")
         ops.STATS.kernel_launches += 1
+        mark()                                      # reduce + scale + broadcast kernel
         hdl.barrier(channel=0)                      # every rank's slice of the result has landed everywhere
         _mark_done(state, buf, ready, side)
+        if marks is not None:
+            state.phases.append((ready, *marks, state.timeline[-1][1], n * 2))
         fut = torch.futures.Future(devices=[buf.device])
         fut.set_result(view)
     return fut

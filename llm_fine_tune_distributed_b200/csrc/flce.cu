@@ -684,21 +684,23 @@ using namespace b200;
 namespace {
 
 // Tuning switches, read from the environment at each call (measurement aid; the defaults are what ships):
-//   B200SFT_L2_HINTS=0      TMA loads without eviction-priority hints
+//   B200SFT_L2_HINTS=mask   bit 0: evict_last on the operand every tile re-reads; bit 1: evict_first on the operand
+//                           that is streamed once (0 = TMA loads without eviction-priority hints)
 //   B200SFT_DX_KS_MAJOR=0   dX work units tile-major (the round-1 order) instead of K-split-major
 //   B200SFT_DX_MIN_SPLITS=n force at least n K-splits of the dX GEMM (power of two); B200SFT_DX_MAX_SPLITS=n the cap (4)
 int tune_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return (v != nullptr && *v != 0) ? atoi(v) : dflt;
 }
-bool l2_hints_on() { return tune_int("B200SFT_L2_HINTS", 1) != 0; }
+uint64_t keep_policy() { return (tune_int("B200SFT_L2_HINTS", 1) & 1) ? L2_EVICT_LAST : 0; }
+uint64_t stream_policy() { return (tune_int("B200SFT_L2_HINTS", 1) & 2) ? L2_EVICT_FIRST : 0; }
 
 // Logit GEMMs (forward, dlogits recompute): X is swept by every vocabulary panel of a rasterisation group, so it is
 // the operand to keep in the L2; W panels are read once per group.
 GemmOpts logit_gemm_opts(const int32_t* n_rows_dev) {
   GemmOpts o;
   o.dyn_rows = n_rows_dev;
-  if (l2_hints_on()) o.a_l2_policy = L2_EVICT_LAST;
+  o.a_l2_policy = keep_policy();
   return o;
 }
 
@@ -985,7 +987,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     ox.max_k_splits = dx_splits;
     ox.min_k_splits = dx_min_splits;
     ox.ks_major = tune_int("B200SFT_DX_KS_MAJOR", 1);
-    if (l2_hints_on()) ox.a_l2_policy = L2_EVICT_FIRST, ox.b_l2_policy = L2_EVICT_LAST;
+    ox.a_l2_policy = stream_policy();
+    ox.b_l2_policy = keep_policy();
     rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream, ox);
     if (rc != 0) return rc;
     }
@@ -1003,7 +1006,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     GemmOpts ow;  // every wave of vocabulary tiles contracts over all of X: keep X, let dlogits stream past it
     ow.dyn_rows = n_rows_dev;
     ow.dyn_is_k = 1;
-    if (l2_hints_on()) ow.a_l2_policy = L2_EVICT_FIRST, ow.b_l2_policy = L2_EVICT_LAST;
+    ow.a_l2_policy = stream_policy();
+    ow.b_l2_policy = keep_policy();
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, ow);
     if (rc != 0) return rc;
   }

@@ -802,18 +802,16 @@ int dx_max_k_splits(int N, int H) {
   return tiles >= 16LL * workers ? 1 : tune_int("B200SFT_DX_MAX_SPLITS", 4);
 }
 
-// With split-major order the tiles in flight share one K range of W[slab] (slab_cols / splits vocabulary rows of
-// H bf16 each); at least this many splits keep that range within DX_W_RANGE_L2_BYTES so it survives in the L2
-// from one wave of M tiles to the next.  Never more than dx_max_k_splits (each split owns an fp32 [N,H] buffer).
-constexpr size_t DX_W_RANGE_L2_BYTES = size_t(72) << 20;
+// Lower bound on the dX K-splits (tuning switch only).  Measured on B200 at N = 8192 (profiles/r02_bwd_tuning.md):
+// split-major order with the 2 splits the fill rule picks cuts the dX GEMM's DRAM reads from 3.1-3.2 GB to
+// 2.2-2.3 GB per 64 Ki-column slab and its time from 1.46 to 1.41 ms, exactly the traffic of "the tiles in flight
+// share their operands, nothing survives from one wave to the next"; forcing 4 or 8 splits to make the W range
+// small enough to survive between waves did not lower the reads further and costs an fp32 [N,H] buffer per split.
 int dx_min_k_splits(int N, int H, int slab_cols) {
+  (void)slab_cols;
   const int maxs = dx_max_k_splits(N, H);
   const int forced = tune_int("B200SFT_DX_MIN_SPLITS", 0);
-  if (forced > 0) return forced < maxs ? forced : maxs;
-  if (tune_int("B200SFT_DX_KS_MAJOR", 1) == 0) return 1;
-  int s = 1;
-  while (s < maxs && static_cast<size_t>(slab_cols) * H * 2 / s > DX_W_RANGE_L2_BYTES) s *= 2;
-  return s;
+  return forced > 0 ? (forced < maxs ? forced : maxs) : 1;
 }
 
 }  // namespace

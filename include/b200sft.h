@@ -271,6 +271,30 @@ int b200sft_allreduce_scale_bf16_p2p(const uint64_t* peer_ptrs_host, size_t n, i
                                      void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Tied-embedding gradient exchanged as rows.  lm_head.weight is embed_tokens.weight
+ * (SP/transformers/models/smollm3/modeling_smollm3.py:367,447) and is trained (training.py:136-141); the
+ * embedding's part of its gradient -- autograd's embedding_dense_backward of `self.embed_tokens(input_ids)`
+ * (modeling_smollm3.py:396), the last op of backward() -- is what keeps DDP from reducing that parameter's
+ * 521 MiB bucket before backward() ends (training.py:249-256; default_hooks.py:18-32).  This call replaces that
+ * op AND the cross-rank averaging of its result: every rank publishes its token ids and the gradient rows dY
+ * w.r.t. the embedding output (symmetric memory, or plain device memory at world 1), then each rank adds
+ *   grad[v,:] = bf16(grad[v,:] + scale * sum_{r, t: ids_r[t] == v} dY_r[t,:])          (fp32 sum)
+ * for the touched rows only, in ONE fixed order (rank, then position) on every rank, so replicas stay bit-identical.
+ * The dense head part of the gradient is then free to go through the bucket hook at the START of backward.
+ *   ids_ptrs_host, dy_ptrs_host, n_ptrs_host   HOST arrays of `world` device pointers: rank r's int32 ids [cap]
+ *            (negative id = skip: padding position, or nn.Embedding's padding_idx), its bf16 dY [cap,H] and an
+ *            int32 device scalar with the number of valid entries (<= cap); peers' pointers are read with plain
+ *            loads over NVLink -- the caller orders the ranks (barrier before: all published; after: all done)
+ *   grad     [V,H] bf16 in/out (the tied weight's gradient after DDP has finalised the backward)
+ *   scale    1/world for DDP's average (the loss already carries compute_loss's x num_processes)
+ * H a multiple of 8, at most 8192; world <= 16.
+ */
+size_t b200sft_embed_grad_workspace_bytes(int world, int cap, int V, int H);
+int b200sft_embed_grad_rows(const uint64_t* ids_ptrs_host, const uint64_t* dy_ptrs_host, const uint64_t* n_ptrs_host,
+                            int world, int cap, int V, int H, float scale, void* grad, void* workspace,
+                            size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Step tail on bf16 parameters: global gradient-norm clip + AdamW as two multi-tensor kernels.
  * Replaces accelerator.clip_grad_norm_(params, max_grad_norm=1.0) (training.py:264 ->
  * SP/transformers/trainer.py:2489-2499 -> torch.nn.utils.clip_grad_norm_) and torch.optim.AdamW.step on

@@ -59,6 +59,9 @@ SIGNATURES = {
                                         c_float, c_float, c_float, c_int, c_float, c_void_p, c_void_p]),
     "b200sft_allreduce_scale_bf16_multimem": (c_int, [c_void_p, c_size_t, c_int, c_int, c_float, c_void_p]),
     "b200sft_allreduce_scale_bf16_p2p": (c_int, [c_void_p, c_size_t, c_int, c_int, c_float, c_void_p]),
+    "b200sft_embed_grad_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200sft_embed_grad_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
+                                        c_void_p, c_size_t, c_void_p]),
 }
 
 _lib = None

@@ -14,7 +14,7 @@ from pathlib import Path
 PKG_DIR = Path(__file__).resolve().parent
 CSRC = PKG_DIR / "csrc"
 LIB_PATH = PKG_DIR / "libb200sft.so"
-SOURCES = ["flce.cu", "elementwise.cu", "rmsnorm.cu", "nvl_allreduce.cu", "optim.cu"]
+SOURCES = ["flce.cu", "elementwise.cu", "rmsnorm.cu", "nvl_allreduce.cu", "optim.cu", "embed_grad.cu"]
 HEADERS = ["sm100_ptx.cuh", "gemm_engine.cuh", "capi_common.h", "../../include/b200sft.h"]
 
 NVCC_FLAGS = [

@@ -258,6 +258,13 @@ def run_b200(args) -> dict:
             hook_state = B200HookState(None)
             wrapped.register_comm_hook(hook_state, b200_allreduce_hook)
         wrapped._b200sft_hook = True
+        if args.tied_exchange == "on" or (args.tied_exchange == "auto" and args.comm == "nvlink"):
+            from llm_fine_tune_distributed_b200.tied_embedding import TiedEmbeddingExchange
+
+            wrapped._b200sft_tied_exchange = TiedEmbeddingExchange(wrapped, max_tokens=B * T)
+            args.tied_exchange = "on"
+        else:
+            args.tied_exchange = "off"
     params = [p for p in model.parameters() if p.requires_grad]
     if stock:
         args.tail = "torch"
@@ -361,13 +368,20 @@ def run_b200(args) -> dict:
         hook_state.timeline = []
         hook_state.phases = []
         bwd_done.clear()
+        if getattr(wrapped, "_b200sft_tied_exchange", None) is not None:
+            wrapped._b200sft_tied_exchange.events = []
     ms_step, wall_dev, _ = timed(args.steps, e2e=False, first_step=100)
     comm_times = None
     if bwd_done is not None and hook_state.timeline:
         # per step: buckets in arrival order; the last one is handed over when backward compute ends, so the time
         # from that hand-over to the end of backward() is communication the step could not hide
         tl, per = hook_state.timeline, len(hook_state.timeline) // max(len(bwd_done), 1)
-        exposed = [tl[(i + 1) * per - 1][0].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
+        tied = getattr(wrapped, "_b200sft_tied_exchange", None)
+        if tied is not None and tied.events and len(tied.events) == len(bwd_done):
+            # the tied bucket left early: backward compute ends when the embedding-output gradient is captured
+            exposed = [tied.events[i][0].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
+        else:
+            exposed = [tl[(i + 1) * per - 1][0].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
         busy = [sum(a.elapsed_time(b) for a, b, _ in tl[i * per:(i + 1) * per]) for i in range(len(bwd_done))]
         big = max(tl, key=lambda t: t[2])
         ph = hook_state.phases
@@ -390,7 +404,8 @@ def run_b200(args) -> dict:
             after = [last_rows[i][5].elapsed_time(bwd_done[i]) for i in range(len(bwd_done))]
             breakdown = {"last_bucket_rank0": mine, "last_bucket_max_over_ranks": dict(zip(names, [round(v, 3) for v in hi.tolist()])),
                          "last_bucket_min_over_ranks": dict(zip(names, [round(v, 3) for v in lo.tolist()])),
-                         "copy_back_and_finalize_ms": round(sum(after) / len(after), 3),
+                         # with the tied exchange the last bucket is done mid-backward: see comm.tied_rows instead
+                         "copy_back_and_finalize_ms": None if tied is not None else round(sum(after) / len(after), 3),
                          "all_buckets_rank0": phase_ms(ph),
                          "note": "per optimizer step; phases of the hook on the side stream: queue = bucket ready -> side stream "
                                  "free; copy_in = staging into the symmetric arena; wait_for_peers = first barrier; kernel = "
@@ -403,6 +418,15 @@ def run_b200(args) -> dict:
                                          "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1)}}
         if breakdown:
             comm_times["breakdown"] = breakdown
+        if tied is not None and tied.events:
+            ev = tied.events
+            comm_times["tied_rows"] = {
+                "publish_ms": round(sum(e[0].elapsed_time(e[1]) for e in ev) / len(ev), 3),
+                "finalize_wait_and_exchange_ms": round(sum(e[1].elapsed_time(e[2]) for e in ev) / len(ev), 3),
+                "note": "per optimizer step, after backward compute: copy of (ids, dY) into symmetric memory; then DDP's "
+                        "finalisation (waits for every bucket, copies results into .grad), barrier, row kernel, barrier"}
+            comm_times["exposed_definition"] = "embedding-output gradient captured (end of backward compute) -> backward() returns"
+            tied.events = None
         hook_state.timeline = None
     launches = ops.STATS.kernel_launches
     fwd_ms, bwd_ms = ops.STATS.mean_ms("flce_fwd"), ops.STATS.mean_ms("flce_bwd")
@@ -528,6 +552,7 @@ def run_b200(args) -> dict:
     if hook_state is not None:
         n_steps = args.steps * (1 if args.no_e2e else 2) + max(args.warmup, 3)
         res["comm"] = {"hook": args.comm, "path": getattr(hook_state, "path_used", "nccl"),
+                       "tied_exchange": args.tied_exchange,
                        "buckets_per_step": round(hook_state.buckets_seen / max(n_steps, 1), 2),
                        "bytes_reduced_per_step": round(hook_state.bytes_reduced / max(n_steps, 1))}
         if comm_times:
@@ -646,6 +671,9 @@ def main():
                     help="N>1: gradient hook.  nvlink = this library's fused NVLink reduce+scale kernel over symmetric "
                          "memory; nccl = scale kernel + NCCL allreduce; auto (default) = nvlink when symmetric memory "
                          "can be set up on every rank, else nccl.  Env B200SFT_COMM overrides.")
+    ap.add_argument("--tied-exchange", default="auto", choices=["auto", "on", "off"],
+                    help="N>1: split the tied lm_head/embed_tokens gradient so its 521 MiB bucket is reduced at the start of "
+                         "backward and only the embedding's rows are exchanged at the end (auto = on with the NVLink hook)")
     ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
                     help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
     ap.add_argument("--cpu-tokens", type=int, default=1024,

@@ -243,6 +243,9 @@ class FusedCELossMixin:
     b200sft_fuse_final_norm: Optional[bool] = None  # final RMSNorm inside the head's row gather: None = when it applies
     b200sft_register_comm_hook: bool = True
     b200sft_nvlink_hook: bool = False  # True (or env B200SFT_COMM=nvlink): the fused NVLink reduce+scale kernel
+    # > 0: under DDP, split the tied lm_head / embed_tokens gradient (tied_embedding.py) so that its bucket is reduced
+    # at the start of backward; the value bounds the tokens of one micro-batch (per-device batch x sequence length)
+    b200sft_tied_exchange_tokens: int = 0
 
     def _b200sft_prepare(self, model: nn.Module) -> None:
         inner = _unwrap(model)
@@ -262,6 +265,12 @@ class FusedCELossMixin:
             # rendezvous of the NVLink hook needs
             register_b200_comm_hook(model, nvlink_kernel=nvlink)
             model._b200sft_hook = True
+        if (self.b200sft_tied_exchange_tokens > 0 and isinstance(model, nn.parallel.DistributedDataParallel)
+                and getattr(model, "_b200sft_tied_exchange", None) is None):
+            from .tied_embedding import TiedEmbeddingExchange
+
+            # allocates and exchanges symmetric memory: a collective, reached at the same point on every rank
+            model._b200sft_tied_exchange = TiedEmbeddingExchange(model, self.b200sft_tied_exchange_tokens)
 
     def _b200sft_num_processes(self) -> int:
         acc = getattr(self, "accelerator", None)
@@ -282,6 +291,9 @@ class FusedCELossMixin:
             kwargs["num_items_in_batch"] = num_items_in_batch
         inputs = dict(inputs)
         plan = inputs.pop("b200sft_plan", None)  # labels built on the device ahead of the forward
+        exchange = getattr(model, "_b200sft_tied_exchange", None)
+        if exchange is not None:  # tied-embedding gradient split: padded positions carry no embedding gradient
+            exchange.set_attention_mask(inputs.get("attention_mask"))
         with fused_head_armed(model, plan):
             outputs = model(**{**inputs, **kwargs})
         if isinstance(outputs, dict) and "loss" not in outputs:

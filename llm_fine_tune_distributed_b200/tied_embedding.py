@@ -108,6 +108,10 @@ class TiedEmbeddingExchange:
         self.exchanges = 0            # synchronising backwards that went through the row exchange
         self._attention_mask = None   # set per forward by the loss seam (padding positions carry no gradient)
         self._pending = None
+        # measurement aid: when a list, every exchange appends CUDA events (dY captured = backward compute is over,
+        # rows published, exchange applied) recorded on the current stream
+        self.events = None
+        self._marks = None
         self._handle = emb.register_forward_hook(self._forward_hook)
 
     def remove(self) -> None:
@@ -144,7 +148,10 @@ class TiedEmbeddingExchange:
     # ---- backward: publish the rows when they exist, apply them after DDP has finalised -------------------
     def _capture(self, ids32: torch.Tensor, grad_out: torch.Tensor, leaf: torch.Tensor) -> None:
         dy = grad_out if grad_out.dtype == torch.bfloat16 else grad_out.to(torch.bfloat16)
+        self._marks = [self._mark()] if self.events is not None and dy.is_cuda else None
         self.transport.publish(ids32, dy.contiguous())
+        if self._marks is not None:
+            self._marks.append(self._mark())
         self._pending = leaf
         torch.autograd.Variable._execution_engine.queue_callback(self._requeue)
         return None
@@ -165,3 +172,12 @@ class TiedEmbeddingExchange:
             raise RuntimeError("tied weight has no gradient after backward: was the head's backward skipped?")
         self.transport.apply(grad, 1.0 / self.world)
         self.exchanges += 1
+        if self._marks is not None:
+            self.events.append((*self._marks, self._mark()))
+            self._marks = None
+
+    @staticmethod
+    def _mark() -> "torch.cuda.Event":
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        return ev

@@ -361,6 +361,9 @@ class MiniSFTTrainer(FusedCELossMixin):
 
                 self.model_wrapped.register_comm_hook(comm_hook_state, b200_allreduce_hook)
                 self.model_wrapped._b200sft_hook = True
+            if os.getenv("TIED_EXCHANGE", "0") == "1" and self.device.type == "cuda":
+                # reduce the tied head/embedding bucket at the start of backward (tied_embedding.py)
+                self.b200sft_tied_exchange_tokens = args.per_device_train_batch_size * args.max_seq_length
         self.train_batches, self.eval_batches = train_batches, eval_batches
         params = [p for p in self.model.parameters() if p.requires_grad]
         self.fused_tail = self.device.type == "cuda" and all(p.dtype == torch.bfloat16 for p in params)

@@ -116,13 +116,13 @@ def test_rows_kernel_rejects_bad_arguments(cuda_device):
     assert lib.b200sft_embed_grad_rows(None, one, one, 1, 8, 16, 16, 1.0, t.data_ptr(), t.data_ptr(), 1 << 20, s) != 0
 
 
-def _ddp_worker(rank, port, ret):
+def _ddp_worker(rank, port, ret, world=1):
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK="0", WORLD_SIZE="1")
-    torch.cuda.set_device(0)
-    dev = torch.device("cuda", 0)
-    dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     from torch.nn.parallel import DistributedDataParallel as DDP
     from transformers import SmolLM3Config, SmolLM3ForCausalLM
 
@@ -139,10 +139,10 @@ def _ddp_worker(rank, port, ret):
         torch.manual_seed(0)
         model = SmolLM3ForCausalLM(cfg).to(torch.bfloat16).to(dev)
         apply_freeze_policy(model)
-        ddp = DDP(model, device_ids=[0], bucket_cap_mb=1)
+        ddp = DDP(model, device_ids=[rank], bucket_cap_mb=1)
 
         class Seam(FusedCELossMixin):
-            num_processes = 1
+            num_processes = world
             model_accepts_loss_kwargs = True
             args = None
             b200sft_register_comm_hook = False
@@ -152,13 +152,15 @@ def _ddp_worker(rank, port, ret):
         ex = TiedEmbeddingExchange(ddp, max_tokens=4 * 64) if split else None
         if ex is not None:
             ddp._b200sft_tied_exchange = ex
-        g = torch.Generator().manual_seed(5)
+        g = torch.Generator().manual_seed(5 + rank)
         for it in range(3):
             a = torch.randint(0, 4096, (4, 64), generator=g).to(dev)
             b = torch.randint(0, 200, (4, 64), generator=g).to(dev)
             mask = torch.ones_like(b)
             mask[2, 50:] = 0
             n_items = (a.ne(-100).sum() + mask.sum()).to(dev)
+            if world > 1:
+                dist.all_reduce(n_items)
             with ddp.no_sync():
                 seam.compute_loss(ddp, {"input_ids": a, "labels": a}, num_items_in_batch=n_items).backward()
             lab = torch.where(mask.bool(), b, torch.full_like(b, -100))
@@ -170,7 +172,10 @@ def _ddp_worker(rank, port, ret):
     ours, exchanges, state = run(True)
     tied = "model.embed_tokens.weight"
     a, b = stock[tied].float(), ours[tied].float()
-    ret[0] = {"exchanges": exchanges, "others_equal": all(torch.equal(stock[k], ours[k]) for k in stock if k != tied),
+    gathered = [torch.zeros_like(b) for _ in range(world)]
+    dist.all_gather(gathered, b.contiguous())
+    ret[rank] = {"exchanges": exchanges, "others_equal": all(torch.equal(stock[k], ours[k]) for k in stock if k != tied),
+              "replicas_identical": all(torch.equal(gathered[0], t) for t in gathered[1:]),
               "rel_err": float((a - b).abs().max() / a.abs().max()),
               "cos": float((a.flatten().double() @ b.flatten().double()) / (a.double().norm() * b.double().norm())),
               "path": state.path_used}
@@ -185,3 +190,17 @@ def test_split_under_world1_nccl_ddp_matches_stock(cuda_device):
           f"max-rel-err {r['rel_err']:.3e}, cos {r['cos']:.6f}")
     assert r["exchanges"] == 3 and r["others_equal"]
     assert r["cos"] >= 0.9999 and r["rel_err"] <= 2.0 ** -6
+
+
+def test_split_under_two_gpu_nccl_ddp_matches_stock():
+    """Two real ranks: rows cross NVLink through the peers' symmetric-memory pointers."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ret = mp.Manager().dict()
+    mp.spawn(_ddp_worker, args=(29693, ret, 2), nprocs=2, join=True)
+    for rank in range(2):
+        r = ret[rank]
+        print(f"rank {rank}: tied gradient, split path vs stock DDP (2 GPUs, NVLink hook {r['path']}): "
+              f"max-rel-err {r['rel_err']:.3e}, cos {r['cos']:.6f}")
+        assert r["exchanges"] == 3 and r["others_equal"] and r["replicas_identical"]
+        assert r["cos"] >= 0.9999 and r["rel_err"] <= 2.0 ** -6

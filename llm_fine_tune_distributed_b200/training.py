@@ -19,7 +19,9 @@ import contextlib
 import json
 import math
 import os
+import re
 import time
+import zlib
 from dataclasses import dataclass, field
 from typing import Any, Callable, Dict, Iterator, List, Optional, Sequence
 
@@ -169,15 +171,22 @@ def format_prompt(example: Dict[str, str]) -> Dict[str, Any]:
 
 
 class ByteChatTokenizer:
-    """Deterministic stand-in used when the SmolLM3 tokenizer cannot be fetched (no network):
-    ChatML-style framing, UTF-8 bytes offset into the vocabulary.  Only shapes and masking matter
-    for the hot path; real runs pass a HF tokenizer instead."""
+    """Deterministic stand-in used when the SmolLM3 tokenizer cannot be fetched (no network): ChatML-style framing;
+    the text is cut into pieces of at most four word characters (with their leading space) or one punctuation /
+    whitespace character, and each piece's UTF-8 bytes are hashed (CRC-32) into the vocabulary.  That gives about one
+    token per 3.5 characters, the scale of a BPE vocabulary, so that the reference's full system prompt
+    (training.py:176-186, ~1,500 characters) takes ~400 of the 1,024 positions as it does with the real tokenizer
+    instead of all of them.  Only shapes and masking matter for the hot path; real runs pass a HF tokenizer."""
 
     pad_token_id = 0
     eos_token_id = 1
+    _PIECES = re.compile(r" ?\w{1,4}| ?[^\w\s]|\s", re.UNICODE)
 
     def __init__(self, vocab_size: int = 128256):
         self.vocab_size = vocab_size
+
+    def encode(self, text: str) -> List[int]:
+        return [2 + zlib.crc32(p.encode("utf-8")) % (self.vocab_size - 2) for p in self._PIECES.findall(text)]
 
     def apply_chat_template(self, messages: List[Dict[str, str]], return_assistant_mask: bool = False):
         """Token ids of the templated conversation; with ``return_assistant_mask`` also a 0/1 list
@@ -185,9 +194,9 @@ class ByteChatTokenizer:
         ids: List[int] = []
         mask: List[int] = []
         for m in messages:
-            head = f"<|im_start|>{m['role']}\n".encode("utf-8")
-            body = f"{m['content']}<|im_end|>\n".encode("utf-8")
-            ids.extend(2 + (b % (self.vocab_size - 2)) for b in head + body)
+            head = self.encode(f"<|im_start|>{m['role']}\n")
+            body = self.encode(f"{m['content']}<|im_end|>\n")
+            ids.extend(head + body)
             mask.extend([0] * len(head) + [1 if m["role"] == "assistant" else 0] * len(body))
         ids.append(self.eos_token_id)
         mask.append(1)

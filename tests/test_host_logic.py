@@ -97,8 +97,12 @@ def test_collate_and_settings(monkeypatch):
     assert batch["labels"].tolist() == [[5, 6, 7, -100, -100], [8, 9, 10, 11, 12]]
     msgs = format_prompt({"full-question": "q?", "answer": "a."})["messages"]
     assert [m["role"] for m in msgs] == ["system", "user", "assistant"]
-    ids = ByteChatTokenizer(128256).apply_chat_template(msgs)
-    assert ids[-1] == 1 and max(ids) < 128256
+    ids, mask = ByteChatTokenizer(128256).apply_chat_template(msgs, return_assistant_mask=True)
+    assert ids[-1] == 1 and max(ids) < 128256 and len(mask) == len(ids)
+    # the reference's full system prompt (training.py:176-186) must leave room for the answer inside max_seq_length:
+    # a sample cut off inside the prompt would have no assistant token left for completion-only loss
+    assert msgs[0]["content"].startswith("You are a wilderness survival") and "Essential Knots" in msgs[0]["content"]
+    assert 300 < len(ids) < 800 and sum(mask[:1024]) >= 3
 
     monkeypatch.setenv("BATCH_SIZE", "28")
     monkeypatch.setenv("LEARNING_RATE", "1e-4")
@@ -134,7 +138,7 @@ def test_completion_only_masks():
     msgs = format_prompt({"full-question": "q?", "answer": "an answer"})["messages"]
     ids, mask = tok.apply_chat_template(msgs, return_assistant_mask=True)
     assert ids == tok.apply_chat_template(msgs) and len(ids) == len(mask)
-    n_assistant = len("an answer<|im_end|>\n".encode()) + 1           # assistant body + eos
+    n_assistant = len(tok.encode("an answer<|im_end|>\n")) + 1        # assistant body + eos
     assert sum(mask) == n_assistant and mask[-1] == 1 and mask[0] == 0
     batch = collate([ids], pad_id=0, max_len=4096, masks=[mask])
     assert int((batch["labels"] != -100).sum()) == n_assistant

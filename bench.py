@@ -56,13 +56,13 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
-        self.gpu_index, self.proc, self.lines = gpu_index, None, []
+    def __init__(self, gpu_index: int, interval_ms: int = 200):
+        self.gpu_index, self.proc, self.lines, self.interval_ms = gpu_index, None, [], interval_ms
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
+                                          "-lms", str(self.interval_ms), "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()

@@ -145,6 +145,7 @@ def synthetic_window(step: int, ga: int, B: int, T: int, pin: bool, workload: st
     """GA micro-batches as dicts of host tensors (pinned when ``pin``).
 
     full   -- full-length rows: ids ~ U[0,V), labels = ids (every position trains).
+    completion -- full-length rows, the first 60 % of every row is prompt (labels -100): completion-only SFT.
     padded -- the reference collator's shape: variable-length rows right-padded to T, attention_mask 0
               and labels -100 on the padding (the only mask the reference produces).
     packed -- BASELINE config 5: variable-length samples packed into rows of T tokens, flattened to
@@ -156,6 +157,8 @@ def synthetic_window(step: int, ga: int, B: int, T: int, pin: bool, workload: st
     for _ in range(ga):
         ids = torch.randint(0, V, (B, T), generator=g, dtype=torch.int64)
         mb = {"input_ids": ids, "labels": ids.clone()}
+        if workload == "completion":
+            mb["labels"][:, : int(0.6 * T)] = -100
         if workload == "padded":
             lens = _sample_lengths(g, B, 48, T)
             mask = (torch.arange(T)[None, :] < torch.tensor(lens)[:, None]).long()
@@ -459,6 +462,11 @@ def run_b200(args) -> dict:
         return float(t)
 
     trained_dev, valid_dev = (all_ranks(v) for v in token_counts[100])
+    per_rank = torch.tensor([token_counts[100][1] / args.steps], device=dev, dtype=torch.float64)  # valid-label tokens / step
+    rank_hi, rank_lo = per_rank.clone(), per_rank.clone()
+    if world > 1:
+        dist.all_reduce(rank_hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rank_lo, op=dist.ReduceOp.MIN)
     if args.kernel_table and rank == 0:
         from torch.profiler import ProfilerActivity, profile
 
@@ -509,10 +517,14 @@ def run_b200(args) -> dict:
                         + (f", DDP bucket 50 MiB + {'built-in allreduce' if stock else f'b200 comm hook ({args.comm})'}" if world > 1 else ""),
             "global_batch": B * GA * world, "seq_len": T, "parallelism": f"dp{world}", "attn": attn,
             "rows": {"full": "full-length rows, every position trains",
+                     "completion": "full-length rows, first 60 % of each row is prompt (labels -100, completion-only loss)",
                      "padded": "variable-length rows right-padded to seq_len (reference collator), -100 on padding",
                      "packed": "variable-length samples packed to seq_len, flattened [1, B*T], restarting position_ids, "
                                "-100 at sample starts, FA2 varlen"}[args.workload],
             "tokens_per_step": round(tokens_per_step, 1), "valid_label_tokens_per_step": round(valid_dev / args.steps, 1),
+            # load balance of the loss work across ranks (valid-label tokens per optimizer step on one rank)
+            "valid_tokens_per_rank": {"min": round(float(rank_lo), 1), "max": round(float(rank_hi), 1),
+                                      "imbalance": round(float(rank_hi) / max(float(rank_lo), 1.0) - 1.0, 5)},
             "skip_ignored_rows": not stock, "final_norm": "stock" if stock else args.final_norm,
             "layers": model.config.num_hidden_layers, "trainable_params": trainable, "total_params": total,
             "l2": "working set (6.2 GB of weights + activations per pass) far exceeds the 126 MB L2; no explicit flush",
@@ -674,7 +686,7 @@ def main():
     ap.add_argument("--tied-exchange", default="auto", choices=["auto", "on", "off"],
                     help="N>1: split the tied lm_head/embed_tokens gradient so its 521 MiB bucket is reduced at the start of "
                          "backward and only the embedding's rows are exchanged at the end (auto = on with the NVLink hook)")
-    ap.add_argument("--workload", default="full", choices=["full", "padded", "packed"],
+    ap.add_argument("--workload", default="full", choices=["full", "completion", "padded", "packed"],
                     help="full = headline (configs 1-3); packed with --batch 2 --seq 4096 = BASELINE config 5")
     ap.add_argument("--cpu-tokens", type=int, default=1024,
                     help="CPU baseline / reference arm: tokens in the bounded sample (one row of the workload by default)")

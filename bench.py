@@ -423,11 +423,20 @@ def run_b200(args) -> dict:
             comm_times["breakdown"] = breakdown
         if tied is not None and tied.events:
             ev = tied.events
+            seg = lambda i: round(sum(e[i].elapsed_time(e[i + 1]) for e in ev) / len(ev), 3)
+            mine = {"publish_ms": seg(0), "ddp_finalize_ms": seg(1), "wait_for_peers_ms": seg(2), "row_kernels_ms": seg(3),
+                    "barrier_after_ms": seg(4)}
+            vec = torch.tensor(list(mine.values()), device=dev, dtype=torch.float64)
+            hi, lo = vec.clone(), vec.clone()
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
             comm_times["tied_rows"] = {
-                "publish_ms": round(sum(e[0].elapsed_time(e[1]) for e in ev) / len(ev), 3),
-                "finalize_wait_and_exchange_ms": round(sum(e[1].elapsed_time(e[2]) for e in ev) / len(ev), 3),
-                "note": "per optimizer step, after backward compute: copy of (ids, dY) into symmetric memory; then DDP's "
-                        "finalisation (waits for every bucket, copies results into .grad), barrier, row kernel, barrier"}
+                "rank0": mine, "max_over_ranks": dict(zip(mine, [round(v, 3) for v in hi.tolist()])),
+                "min_over_ranks": dict(zip(mine, [round(v, 3) for v in lo.tolist()])),
+                "note": "per optimizer step, after backward compute: publish = copy of (ids, dY) into symmetric memory; "
+                        "ddp_finalize = DDP waits for every bucket and copies the results into .grad; wait_for_peers = first "
+                        "barrier (rank skew: the early ranks wait here for the late ones); row_kernels = the six kernels of "
+                        "b200sft_embed_grad_rows; barrier_after = second barrier"}
             comm_times["exposed_definition"] = "embedding-output gradient captured (end of backward compute) -> backward() returns"
             tied.events = None
         hook_state.timeline = None

@@ -67,17 +67,22 @@ class SymmetricRowTransport:
         self.dy_view[:n].copy_(dy.reshape(n, self.hidden))
         self.n_view.fill_(n)
 
-    def apply(self, grad: torch.Tensor, scale: float) -> None:
+    def apply(self, grad: torch.Tensor, scale: float, mark: Optional[Callable[[], None]] = None) -> None:
+        """``mark`` (measurement aid) is called after the first barrier and after the kernels."""
         from . import ops
 
         stream = torch.cuda.current_stream(self.device)
         with torch.cuda.device(self.device):
             self.handle.barrier(channel=1)            # every rank has published its rows
+            if mark is not None:
+                mark()
             _cabi.check(_cabi.load().b200sft_embed_grad_rows(self._ids_ptrs, self._dy_ptrs, self._n_ptrs, self.world,
                                                              self.cap, self.vocab, self.hidden, float(scale),
                                                              grad.data_ptr(), self.workspace.data_ptr(), self.ws_bytes,
                                                              stream.cuda_stream), "b200sft_embed_grad_rows")
             ops.STATS.kernel_launches += 6
+            if mark is not None:
+                mark()
             self.handle.barrier(channel=1)            # every rank has read them: the arena may be rewritten
 
 
@@ -108,8 +113,8 @@ class TiedEmbeddingExchange:
         self.exchanges = 0            # synchronising backwards that went through the row exchange
         self._attention_mask = None   # set per forward by the loss seam (padding positions carry no gradient)
         self._pending = None
-        # measurement aid: when a list, every exchange appends CUDA events (dY captured = backward compute is over,
-        # rows published, exchange applied) recorded on the current stream
+        # measurement aid: when a list, every exchange appends six CUDA events recorded on the current stream: dY captured
+        # (= backward compute is over), rows published, DDP finalised, peers arrived, rows added, all ranks done
         self.events = None
         self._marks = None
         self._handle = emb.register_forward_hook(self._forward_hook)
@@ -170,11 +175,14 @@ class TiedEmbeddingExchange:
         grad = self.weight.grad
         if grad is None:
             raise RuntimeError("tied weight has no gradient after backward: was the head's backward skipped?")
-        self.transport.apply(grad, 1.0 / self.world)
-        self.exchanges += 1
-        if self._marks is not None:
+        if self._marks is not None:   # (captured, published, DDP finalised, peers arrived, rows added, all ranks done)
+            self._marks.append(self._mark())
+            self.transport.apply(grad, 1.0 / self.world, mark=lambda: self._marks.append(self._mark()))
             self.events.append((*self._marks, self._mark()))
             self._marks = None
+        else:
+            self.transport.apply(grad, 1.0 / self.world)
+        self.exchanges += 1
 
     @staticmethod
     def _mark() -> "torch.cuda.Event":

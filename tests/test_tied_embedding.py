@@ -95,7 +95,7 @@ class GlooRowTransport:
         rows[:ids32.numel()] = dy.reshape(-1, self.hidden)
         self.mine = (ids, rows)
 
-    def apply(self, grad, scale):
+    def apply(self, grad, scale, mark=None):
         all_ids = [torch.empty_like(self.mine[0]) for _ in range(self.world)]
         all_dy = [torch.empty(self.cap, self.hidden) for _ in range(self.world)]
         dist.all_gather(all_ids, self.mine[0], group=self.group)

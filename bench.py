@@ -415,7 +415,13 @@ def run_b200(args) -> dict:
                                  "reduce+scale+broadcast; barrier_after = second barrier; copy_back_and_finalize = last bucket "
                                  "done -> backward() returns (DDP copies 838 MB of results into .grad)"}
         hook_state.phases = []
+        ex_mine = torch.tensor([sum(exposed) / len(exposed)], device=dev, dtype=torch.float64)
+        ex_hi, ex_lo = ex_mine.clone(), ex_mine.clone()
+        dist.all_reduce(ex_hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ex_lo, op=dist.ReduceOp.MIN)
         comm_times = {"exposed_ms_per_step": round(sum(exposed) / len(exposed), 3),
+                      # the latest rank pays only its own copies and kernels; the others also wait for it (rank skew)
+                      "exposed_ms_per_step_over_ranks": {"min": round(float(ex_lo), 3), "max": round(float(ex_hi), 3)},
                       "hook_busy_ms_per_step": round(sum(busy) / len(busy), 3),
                       "largest_bucket": {"MiB": round(big[2] / 2**20, 1), "ms": round(big[0].elapsed_time(big[1]), 3),
                                          "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1)}}

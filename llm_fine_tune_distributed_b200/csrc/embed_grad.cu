@@ -19,7 +19,8 @@
 // counts, never for values -- and added in fp32 in ascending (rank, position) order:
 //   hist      per 1024-token block b: hist[b][v] = tokens of block b with id v
 //   prefix    per v: exclusive prefix of hist[.][v] over blocks; count[v]
-//   scan      one block: start[v] = exclusive scan of count; list of touched rows; 64-token chunks per row
+//   scan      two kernels over 1024-row tiles: start[v] = exclusive scan of count; list of touched rows; 64-token
+//             chunks per row and the work-item -> row map
 //   place     token j of block b goes to perm[start[v] + hist[b][v] + (tokens with the same id before j in b)]
 //   sum       per (row, chunk): fp32 sum of <= 64 dY rows in perm order; a row with one chunk is finished here
 //   finish    rows with several chunks: chunk partials added in order, then the same update
@@ -46,6 +47,11 @@ struct EgPeers {
   const int32_t* n_tokens[EG_MAX_PEERS];    // device scalar: valid prefix length of rank r's arrays (<= cap)
 };
 
+// One element of the four simultaneous scans over the vocabulary rows: tokens, touched rows, chunks, partial slots.
+struct EgQuad {
+  int tok, row, wrk, par;
+};
+
 struct EgScratch {
   int32_t* hist;     // [n_blocks][V]
   int32_t* count;    // [V]
@@ -53,6 +59,8 @@ struct EgScratch {
   int32_t* rows;     // [V]   touched rows, ascending
   int32_t* wstart;   // [V+1] first work item of touched row u (exclusive scan of its chunk count)
   int32_t* pstart;   // [V+1] first partial-sum slot of touched row u (rows with more than one chunk own slots)
+  int32_t* wrow;     // [max_work] touched-row index u of every work item
+  EgQuad* tile_sums; // [ceil(V / 1024)]
   int32_t* totals;   // [2]   n_rows, n_work
   int32_t* perm;     // [world * cap]
   float* partial;    // [max_partials][H]
@@ -90,59 +98,85 @@ __global__ void eg_prefix_blocks_kernel(int32_t* __restrict__ hist, int n_blocks
 __device__ __forceinline__ int eg_chunks(int c) { return (c + EG_CHUNK - 1) / EG_CHUNK; }
 __device__ __forceinline__ int eg_slots(int c) { return c > EG_CHUNK ? eg_chunks(c) : 0; }
 
-// One block of 1024 threads: four exclusive scans over the V counts (tokens, touched rows, chunks, partial slots).
-__global__ void __launch_bounds__(1024)
-    eg_scan_rows_kernel(const int32_t* __restrict__ count, int V, int32_t* __restrict__ start, int32_t* __restrict__ rows,
-                        int32_t* __restrict__ wstart, int32_t* __restrict__ pstart, int32_t* __restrict__ totals) {
-  __shared__ int s_tok[1024], s_row[1024], s_wrk[1024], s_par[1024];
-  const int per = (V + 1023) / 1024;
-  const int lo = min(threadIdx.x * per, V), hi = min(lo + per, V);
-  int tok = 0, row = 0, wrk = 0, par = 0;
-  for (int v = lo; v < hi; ++v) {
-    const int c = count[v];
-    tok += c;
-    row += c > 0;
-    wrk += eg_chunks(c);
-    par += eg_slots(c);
+// Four exclusive scans over the V counts (tokens, touched rows, 64-token chunks, partial-sum slots), in two parallel
+// kernels over tiles of 1024 vocabulary rows: tile sums first, then every tile adds up the sums of the tiles before it
+// (at most a few hundred values) and scans its own rows.
+__device__ __forceinline__ EgQuad eg_quad(int c) { return EgQuad{c, c > 0 ? 1 : 0, eg_chunks(c), eg_slots(c)}; }
+__device__ __forceinline__ EgQuad operator+(EgQuad a, EgQuad b) {
+  return EgQuad{a.tok + b.tok, a.row + b.row, a.wrk + b.wrk, a.par + b.par};
+}
+__device__ __forceinline__ EgQuad eg_shfl_up(EgQuad q, int d) {
+  return EgQuad{__shfl_up_sync(0xffffffffu, q.tok, d), __shfl_up_sync(0xffffffffu, q.row, d),
+                __shfl_up_sync(0xffffffffu, q.wrk, d), __shfl_up_sync(0xffffffffu, q.par, d)};
+}
+// Inclusive scan across the 1024 threads of a block; returns this thread's inclusive value, *total = block sum.
+__device__ __forceinline__ EgQuad eg_block_scan(EgQuad q, EgQuad* s_warp /*[32]*/, EgQuad* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int d = 1; d < 32; d <<= 1) {
+    const EgQuad o = eg_shfl_up(q, d);
+    if (lane >= d) q = q + o;
   }
-  s_tok[threadIdx.x] = tok;
-  s_row[threadIdx.x] = row;
-  s_wrk[threadIdx.x] = wrk;
-  s_par[threadIdx.x] = par;
+  if (lane == 31) s_warp[warp] = q;
   __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {  // inclusive Hillis-Steele over the 1024 partials
-    int a = 0, b = 0, c = 0, d = 0;
-    if (threadIdx.x >= off)
-      a = s_tok[threadIdx.x - off], b = s_row[threadIdx.x - off], c = s_wrk[threadIdx.x - off], d = s_par[threadIdx.x - off];
-    __syncthreads();
-    s_tok[threadIdx.x] += a;
-    s_row[threadIdx.x] += b;
-    s_wrk[threadIdx.x] += c;
-    s_par[threadIdx.x] += d;
-    __syncthreads();
-  }
-  tok = s_tok[threadIdx.x] - tok;  // exclusive
-  row = s_row[threadIdx.x] - row;
-  wrk = s_wrk[threadIdx.x] - wrk;
-  par = s_par[threadIdx.x] - par;
-  for (int v = lo; v < hi; ++v) {
-    const int c = count[v];
-    start[v] = tok;
-    tok += c;
-    if (c > 0) {
-      rows[row] = v;
-      wstart[row] = wrk;
-      pstart[row] = par;
-      ++row;
-      wrk += eg_chunks(c);
-      par += eg_slots(c);
+  if (warp == 0) {
+    EgQuad w = s_warp[lane];
+    for (int d = 1; d < 32; d <<= 1) {
+      const EgQuad o = eg_shfl_up(w, d);
+      if (lane >= d) w = w + o;
     }
+    s_warp[lane] = w;
   }
-  if (threadIdx.x == 1023) {
-    totals[0] = s_row[1023];
-    totals[1] = s_wrk[1023];
-    wstart[s_row[1023]] = s_wrk[1023];  // sentinels: end of the last row's work items / slots
-    pstart[s_row[1023]] = s_par[1023];
+  __syncthreads();
+  if (warp > 0) q = q + s_warp[warp - 1];
+  *total = s_warp[31];
+  return q;
+}
+
+__global__ void __launch_bounds__(1024)
+    eg_tile_sums_kernel(const int32_t* __restrict__ count, int V, EgQuad* __restrict__ tile_sums) {
+  __shared__ EgQuad s_warp[32];
+  const int v = blockIdx.x * 1024 + threadIdx.x;
+  EgQuad total;
+  eg_block_scan(eg_quad(v < V ? count[v] : 0), s_warp, &total);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024)
+    eg_scan_rows_kernel(const int32_t* __restrict__ count, int V, const EgQuad* __restrict__ tile_sums,
+                        int32_t* __restrict__ start, int32_t* __restrict__ rows, int32_t* __restrict__ wstart,
+                        int32_t* __restrict__ pstart, int32_t* __restrict__ wrow, int32_t* __restrict__ totals) {
+  __shared__ EgQuad s_warp[32];
+  __shared__ EgQuad s_base;
+  if (threadIdx.x < 32) {  // sum of the tiles before this one (fixed order; integers)
+    EgQuad b = {0, 0, 0, 0};
+    for (int t = threadIdx.x; t < static_cast<int>(blockIdx.x); t += 32) b = b + tile_sums[t];
+    for (int d = 16; d > 0; d >>= 1)
+      b = b + EgQuad{__shfl_down_sync(0xffffffffu, b.tok, d), __shfl_down_sync(0xffffffffu, b.row, d),
+                     __shfl_down_sync(0xffffffffu, b.wrk, d), __shfl_down_sync(0xffffffffu, b.par, d)};
+    if (threadIdx.x == 0) s_base = b;
+  }
+  __syncthreads();
+  const int v = blockIdx.x * 1024 + threadIdx.x;
+  const int c = v < V ? count[v] : 0;
+  const EgQuad mine = eg_quad(c);
+  EgQuad total;
+  const EgQuad incl = eg_block_scan(mine, s_warp, &total);
+  const EgQuad base = s_base;
+  const int tok = base.tok + incl.tok - mine.tok, row = base.row + incl.row - mine.row;
+  const int wrk = base.wrk + incl.wrk - mine.wrk, par = base.par + incl.par - mine.par;
+  if (v < V) start[v] = tok;
+  if (c > 0) {
+    rows[row] = v;
+    wstart[row] = wrk;
+    pstart[row] = par;
+    for (int k = 0; k < mine.wrk; ++k) wrow[wrk + k] = row;  // work item -> touched row (long only for very frequent tokens)
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 1023) {
+    const EgQuad all = base + total;
+    totals[0] = all.row;
+    totals[1] = all.wrk;
+    wstart[all.row] = all.wrk;  // sentinels: end of the last row's work items / slots
+    pstart[all.row] = all.par;
   }
 }
 
@@ -188,18 +222,13 @@ __global__ void __launch_bounds__(EG_SUM_THREADS)
     eg_sum_chunks_kernel(EgPeers p, int cap, int H, float scale, const int32_t* __restrict__ count,
                          const int32_t* __restrict__ start, const int32_t* __restrict__ rows,
                          const int32_t* __restrict__ wstart, const int32_t* __restrict__ pstart,
-                         const int32_t* __restrict__ totals, const int32_t* __restrict__ perm, float* __restrict__ partial,
-                         __nv_bfloat16* __restrict__ grad) {
-  const int n_rows = totals[0], n_work = totals[1];
+                         const int32_t* __restrict__ wrow, const int32_t* __restrict__ totals,
+                         const int32_t* __restrict__ perm, float* __restrict__ partial, __nv_bfloat16* __restrict__ grad) {
+  const int n_work = totals[1];
   const int nvec = H / 8;
   __shared__ int s_tok[EG_CHUNK];
   for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
-    int lo = 0, hi = n_rows - 1;  // last u with wstart[u] <= w
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (wstart[mid] <= w) lo = mid; else hi = mid - 1;
-    }
-    const int u = lo, row = rows[u], k = w - wstart[u];
+    const int u = wrow[w], row = rows[u], k = w - wstart[u];
     const int L = count[row], first = k * EG_CHUNK, len = min(EG_CHUNK, L - first);
     __syncthreads();  // s_tok of the previous work item is no longer read
     if (threadIdx.x < len) s_tok[threadIdx.x] = perm[start[row] + first + threadIdx.x];
@@ -261,6 +290,12 @@ inline size_t eg_align(size_t x) { return (x + 255) / 256 * 256; }
 
 int eg_blocks_per_rank(int cap) { return (cap + EG_BLOCK_TOKENS - 1) / EG_BLOCK_TOKENS; }
 
+// Work items: ceil(L / EG_CHUNK) per touched row <= tokens / EG_CHUNK + touched rows, touched rows <= min(tokens, V).
+size_t eg_max_work(int world, int cap, int V) {
+  const size_t tokens = static_cast<size_t>(world) * cap;
+  return tokens / EG_CHUNK + (tokens < static_cast<size_t>(V) ? tokens : static_cast<size_t>(V)) + 1;
+}
+
 // Partial-sum slots: only rows with more than EG_CHUNK tokens own any, ceil(L / EG_CHUNK) <= L / EG_CHUNK + 1 each
 // and there are at most tokens / (EG_CHUNK + 1) such rows.
 size_t eg_max_partials(int world, int cap) {
@@ -283,10 +318,12 @@ size_t eg_workspace(int world, int cap, int V, int H, EgScratch* s, void* base) 
   int32_t* rows = reinterpret_cast<int32_t*>(take(static_cast<size_t>(V) * 4));
   int32_t* wstart = reinterpret_cast<int32_t*>(take((static_cast<size_t>(V) + 1) * 4));
   int32_t* pstart = reinterpret_cast<int32_t*>(take((static_cast<size_t>(V) + 1) * 4));
+  int32_t* wrow = reinterpret_cast<int32_t*>(take(eg_max_work(world, cap, V) * 4));
+  EgQuad* tile_sums = reinterpret_cast<EgQuad*>(take(static_cast<size_t>((V + 1023) / 1024) * sizeof(EgQuad)));
   int32_t* totals = reinterpret_cast<int32_t*>(take(16));
   int32_t* perm = reinterpret_cast<int32_t*>(take(static_cast<size_t>(world) * cap * 4));
   float* partial = reinterpret_cast<float*>(take(eg_max_partials(world, cap) * H * sizeof(float)));
-  if (s) *s = EgScratch{hist, count, start, rows, wstart, pstart, totals, perm, partial};
+  if (s) *s = EgScratch{hist, count, start, rows, wstart, pstart, wrow, tile_sums, totals, perm, partial};
   return off;
 }
 
@@ -332,7 +369,11 @@ int b200sft_embed_grad_rows(const uint64_t* ids_ptrs_host, const uint64_t* dy_pt
   B200_CUDA_CHECK(cudaGetLastError());
   eg_prefix_blocks_kernel<<<(V + 255) / 256, 256, 0, stream>>>(s.hist, nb, V, s.count);
   B200_CUDA_CHECK(cudaGetLastError());
-  eg_scan_rows_kernel<<<1, 1024, 0, stream>>>(s.count, V, s.start, s.rows, s.wstart, s.pstart, s.totals);
+  const int v_tiles = (V + 1023) / 1024;
+  eg_tile_sums_kernel<<<v_tiles, 1024, 0, stream>>>(s.count, V, s.tile_sums);
+  B200_CUDA_CHECK(cudaGetLastError());
+  eg_scan_rows_kernel<<<v_tiles, 1024, 0, stream>>>(s.count, V, s.tile_sums, s.start, s.rows, s.wstart, s.pstart, s.wrow,
+                                                    s.totals);
   B200_CUDA_CHECK(cudaGetLastError());
   eg_place_kernel<<<nb, EG_BLOCK_TOKENS, 0, stream>>>(p, cap, bpr, V, s.hist, s.start, s.perm);
   B200_CUDA_CHECK(cudaGetLastError());
@@ -341,7 +382,8 @@ int b200sft_embed_grad_rows(const uint64_t* ids_ptrs_host, const uint64_t* dy_pt
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   if (sms <= 0) sms = 148;
   eg_sum_chunks_kernel<<<sms * 8, EG_SUM_THREADS, 0, stream>>>(p, cap, H, scale, s.count, s.start, s.rows, s.wstart, s.pstart,
-                                                               s.totals, s.perm, s.partial, static_cast<__nv_bfloat16*>(grad));
+                                                               s.wrow, s.totals, s.perm, s.partial,
+                                                               static_cast<__nv_bfloat16*>(grad));
   B200_CUDA_CHECK(cudaGetLastError());
   eg_finish_rows_kernel<<<sms * 4, EG_SUM_THREADS, 0, stream>>>(H, scale, s.count, s.rows, s.pstart, s.totals, s.partial,
                                                                 static_cast<__nv_bfloat16*>(grad));

@@ -351,8 +351,8 @@ def run_b200(args) -> dict:
             if e2e:
                 # D2H of the step's result: every step's summed loss goes to pinned host memory as soon as it exists.
                 # The copy is asynchronous, as a trainer's logging is (Trainer reads tr_loss every logging_steps only,
-                # training.py:266): a blocking .item() per step would drain the launch queue and idle the GPU for
-                # ~15 ms per step.  All of them are on the host, and read, before the timed region ends.
+                # training.py:266): a blocking .item() per step would drain the launch queue at every step boundary.
+                # All of them are on the host, and read, before the timed region ends.
                 host_losses[i].copy_(loss, non_blocking=True)
         ev1.record()
         torch.cuda.synchronize()

@@ -396,6 +396,7 @@ def run_b200(args) -> dict:
         busy = [sum(a.elapsed_time(b) for a, b, _ in tl[i * per:(i + 1) * per]) for i in range(len(bwd_done))]
         big = max(tl, key=lambda t: t[2])
         ph = hook_state.phases
+        big_ph = max(ph, key=lambda r: r[6]) if ph else None   # the reduce kernel of the largest bucket alone
         names = ("queue_ms", "copy_in_ms", "wait_for_peers_ms", "kernel_ms", "barrier_after_ms")
 
         def phase_ms(rows):
@@ -432,7 +433,12 @@ def run_b200(args) -> dict:
                       "exposed_ms_per_step_over_ranks": {"min": round(float(ex_lo), 3), "max": round(float(ex_hi), 3)},
                       "hook_busy_ms_per_step": round(sum(busy) / len(busy), 3),
                       "largest_bucket": {"MiB": round(big[2] / 2**20, 1), "ms": round(big[0].elapsed_time(big[1]), 3),
-                                         "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1)}}
+                                         "bus_GBps": round(2 * (world - 1) / world * big[2] / big[0].elapsed_time(big[1]) / 1e6, 1),
+                                         "note": "ms = hand-over to done, i.e. including the wait for the other ranks at the barrier"}}
+        if big_ph is not None:
+            k_ms = big_ph[3].elapsed_time(big_ph[4])
+            comm_times["largest_bucket"].update({"kernel_ms": round(k_ms, 3),
+                                                 "kernel_bus_GBps": round(2 * (world - 1) / world * big_ph[6] / k_ms / 1e6, 1)})
         if breakdown:
             comm_times["breakdown"] = breakdown
         if tied is not None and tied.events:

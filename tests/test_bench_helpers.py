@@ -55,3 +55,20 @@ def test_clock_sampler_parsing():
 def test_peaks_come_from_measured_file_when_present():
     p = bench.read_peaks()
     assert p["burst"] > 1000 and p["sustained"] <= p["burst"] and p["hbm"] > 1000
+
+
+def test_completion_only_workload_masks_the_prompt():
+    mb = bench.synthetic_window(step=2, ga=1, B=4, T=1000, pin=False, workload="completion")[0]
+    assert "attention_mask" not in mb                                   # full-length rows: every token is trained on
+    assert bool((mb["labels"][:, :600] == -100).all()) and torch.equal(mb["labels"][:, 600:], mb["input_ids"][:, 600:])
+    assert bench.window_tokens([mb]) == (4000, 1600)
+
+
+def test_reference_arm_thread_count_ignores_torchruns_omp_setting(monkeypatch):
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm (rank 0 alone) must still use every core it may
+    run on, and the other ranks must leave without work."""
+    monkeypatch.setenv("OMP_NUM_THREADS", "1")
+    assert bench.host_threads() == len(os.sched_getaffinity(0)) >= 1
+    monkeypatch.setenv("RANK", "3")
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    assert bench.run_reference(type("A", (), {"steps": 5, "warmup": 3, "cpu_tokens": 16})()) == {}

@@ -676,6 +676,9 @@ def main() -> None:  # mirrors training.py:49-349
             "world_size": world_size, "distributed_training": world_size > 1,
             "train_tokens_per_second": getattr(result, "metrics", {}).get("train_tokens_per_second"),
         }
+        exchange = getattr(getattr(trainer, "model_wrapped", None), "_b200sft_tied_exchange", None)
+        if exchange is not None:  # beyond the reference's keys: optimizer steps whose tied gradient went through the split
+            summary["tied_exchange_steps"] = exchange.exchanges
         with open(f"{output_dir}/training_summary.json", "w") as f:
             json.dump(summary, f, indent=2)
     if dist.is_initialized():

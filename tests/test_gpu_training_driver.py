@@ -68,14 +68,15 @@ def test_driver_padding_free_completion_only(cuda_device, tmp_path):
     _check(tmp_path, 1)
 
 
-@pytest.mark.parametrize("comm", ["nccl", "nvlink"])
+@pytest.mark.parametrize("comm", ["nccl", "nvlink", "nvlink+tied"])
 def test_driver_two_gpus_ddp(cuda_device, tmp_path, comm):
+    """nvlink+tied: TIED_EXCHANGE=1 also splits the tied lm_head / embed_tokens gradient (tied_embedding.py)."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     _write_parquet(tmp_path / "qa.parquet")
-    env = _env(tmp_path, B200SFT_COMM=comm)
+    env = _env(tmp_path, B200SFT_COMM=comm.split("+")[0], TIED_EXCHANGE="1" if comm.endswith("tied") else "0")
     for k in ("WORLD_SIZE", "RANK", "LOCAL_RANK"):
         env.pop(k, None)
     res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
@@ -84,6 +85,8 @@ def test_driver_two_gpus_ddp(cuda_device, tmp_path, comm):
                          timeout=400)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
     _check(tmp_path, 2)
+    summary = json.load(open(tmp_path / "out" / "training_summary.json"))
+    assert summary.get("tied_exchange_steps") == (3 if comm.endswith("tied") else None)   # MAX_STEPS=3 optimizer steps
 
 
 @pytest.mark.parametrize("extra", [dict(COMPLETION_ONLY="1"),

@@ -98,6 +98,9 @@ def b200_allreduce_hook(state: B200HookState, bucket: dist.GradBucket) -> torch.
     state.bytes_reduced += buf.numel() * buf.element_size()
 
     def body():
+        # default_hooks.py:25 divides (tensor.div_(world_size)); on CUDA that division by a host scalar IS a multiply by
+        # the fp32 reciprocal (ATen BinaryDivTrueKernel), so scaling by fp32(1/world) gives the reference's bits for
+        # every world size, powers of two or not (tests/test_gpu_allreduce_kernel_one_gpu.py, worlds 2..8)
         state.scale_fn(buf, 1.0 / world)
         return dist.all_reduce(buf, group=group, async_op=True)
 

@@ -7,7 +7,7 @@ N=$1; EXTRA=${2:-}
 mkdir -p gpurun_out
 O=gpurun_out
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 5 --warmup 3"
-CPU="--no-cpu-baseline"; [ "$EXTRA" = "cpu" ] && CPU=""
+CPU="--no-cpu-baseline"; { [ "$EXTRA" = "cpu" ] || [ "$EXTRA" = "cpuonly" ]; } && CPU=""
 $RUN $CPU > $O/r02_bench_${N}gpu.json 2> $O/r02_bench_${N}gpu.err
 $RUN --no-cpu-baseline --workload packed --batch 2 --seq 4096 > $O/r02_bench_packed_${N}gpu.json 2> $O/r02_bench_packed_${N}gpu.err
 if [ "$N" = "8" ] || [ "$EXTRA" = "off" ]; then

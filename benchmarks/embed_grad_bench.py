@@ -50,6 +50,16 @@ def main():
                 e.record()
                 torch.cuda.synchronize()
                 tot += s.elapsed_time(e)
+            if "--kernel-times" in sys.argv:
+                from torch.profiler import ProfilerActivity, profile
+
+                with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                    for _ in range(5):
+                        call()
+                    torch.cuda.synchronize()
+                for ev in sorted(prof.key_averages(), key=lambda e: -e.device_time_total):
+                    if ev.device_time_total > 0:
+                        print(f"   {ev.device_time_total / ev.count:8.1f} us x{ev.count:3d}  {ev.key[:90]}")
             touched = int(torch.unique(torch.cat(ids)).numel())
             moved = world * cap * H * 2 + 2 * touched * H * 2
             # the dense alternative on one rank: embedding backward ([V,H] zeros + index_add) and the add into the gradient

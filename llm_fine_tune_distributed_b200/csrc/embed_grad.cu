@@ -22,7 +22,7 @@
 //   scan      two kernels over 1024-row tiles: start[v] = exclusive scan of count; list of touched rows; 64-token
 //             chunks per row and the work-item -> row map
 //   place     token j of block b goes to perm[start[v] + hist[b][v] + (tokens with the same id before j in b)]
-//   sum       per (row, chunk), one warp each: fp32 sum of <= 64 dY rows in perm order; a row with one chunk is finished here
+//   sum       per (row, chunk): fp32 sum of <= 64 dY rows in perm order; a row with one chunk is finished here
 //   finish    rows with several chunks: chunk partials added in order, then the same update
 // Long segments (a frequent token, many ranks) are split into chunks so that no single thread block walks them alone.
 #include <cuda_bf16.h>
@@ -39,7 +39,7 @@ constexpr int EG_MAX_PEERS = 16;
 constexpr int EG_BLOCK_TOKENS = 1024;  // tokens per histogram block (= threads of hist / place)
 constexpr int EG_CHUNK = 64;           // tokens summed by one work item
 constexpr int EG_SUM_THREADS = 256;
-constexpr int EG_MAX_H = 8192;
+constexpr int EG_MAX_VEC = 4;          // 16-byte column vectors per thread: H <= 256 * 4 * 8 = 8192
 
 struct EgPeers {
   const int32_t* ids[EG_MAX_PEERS];         // [cap] token ids of rank r (negative = skip: padding)
@@ -217,11 +217,7 @@ __device__ __forceinline__ void eg_update8(__nv_bfloat16* g, const float (&a)[8]
   *reinterpret_cast<uint4*>(g) = old;
 }
 
-// One work item = (touched row u, chunk k of its token segment) per WARP: the warp keeps the chunk's <= 64 token indices
-// in registers (two per lane, broadcast with shuffles) and, for 2048 columns at a time, every lane owns eight 16-byte
-// column vectors (lane + 32 i), so each token costs eight independent coalesced 512-byte loads per lane group -- from
-// the peers' memory over NVLink for seven ranks out of eight, hence as many loads in flight as registers allow.
-constexpr int EG_LANE_VECS = 8;                       // 16-byte vectors per lane and pass: 32 * 8 * 8 = 2048 columns
+// One work item = (touched row u, chunk k of its token segment) per block iteration.
 __global__ void __launch_bounds__(EG_SUM_THREADS)
     eg_sum_chunks_kernel(EgPeers p, int cap, int H, float scale, const int32_t* __restrict__ count,
                          const int32_t* __restrict__ start, const int32_t* __restrict__ rows,
@@ -230,46 +226,38 @@ __global__ void __launch_bounds__(EG_SUM_THREADS)
                          const int32_t* __restrict__ perm, float* __restrict__ partial, __nv_bfloat16* __restrict__ grad) {
   const int n_work = totals[1];
   const int nvec = H / 8;
-  const int lane = threadIdx.x & 31;
-  const int warps_per_block = EG_SUM_THREADS / 32;
-  const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5), n_warps = gridDim.x * warps_per_block;
-  for (int w = warp_global; w < n_work; w += n_warps) {
+  __shared__ int s_tok[EG_CHUNK];
+  for (int w = blockIdx.x; w < n_work; w += gridDim.x) {
     const int u = wrow[w], row = rows[u], k = w - wstart[u];
     const int L = count[row], first = k * EG_CHUNK, len = min(EG_CHUNK, L - first);
-    const int base = start[row] + first;
-    const int tok0 = lane < len ? perm[base + lane] : 0;
-    const int tok1 = lane + 32 < len ? perm[base + lane + 32] : 0;
-    const bool whole_row = (L <= EG_CHUNK);
-    for (int v0 = 0; v0 < nvec; v0 += 32 * EG_LANE_VECS) {   // 2048 columns per pass (one pass for H <= 2048)
-      float acc[EG_LANE_VECS][8];
+    __syncthreads();  // s_tok of the previous work item is no longer read
+    if (threadIdx.x < len) s_tok[threadIdx.x] = perm[start[row] + first + threadIdx.x];
+    __syncthreads();
+    float acc[EG_MAX_VEC][8];
 #pragma unroll
-      for (int i = 0; i < EG_LANE_VECS; ++i)
+    for (int i = 0; i < EG_MAX_VEC; ++i)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[i][e] = 0.f;
-      for (int j = 0; j < len; ++j) {  // ascending (rank, position): the one summation order
-        const int tok = __shfl_sync(0xffffffffu, j < 32 ? tok0 : tok1, j & 31);
-        const int r = tok / cap, t = tok - r * cap;
-        const uint4* src = reinterpret_cast<const uint4*>(p.dy[r] + static_cast<size_t>(t) * H);
-        uint4 x[EG_LANE_VECS];
+      for (int e = 0; e < 8; ++e) acc[i][e] = 0.f;
+    for (int j = 0; j < len; ++j) {  // ascending (rank, position): the one summation order
+      const int tok = s_tok[j], r = tok / cap, t = tok - r * cap;
+      const uint4* src = reinterpret_cast<const uint4*>(p.dy[r] + static_cast<size_t>(t) * H);
 #pragma unroll
-        for (int i = 0; i < EG_LANE_VECS; ++i) {  // all loads of the token first, then the adds
-          const int v = v0 + lane + 32 * i;
-          x[i] = v < nvec ? src[v] : make_uint4(0, 0, 0, 0);
-        }
-#pragma unroll
-        for (int i = 0; i < EG_LANE_VECS; ++i) eg_add8(acc[i], x[i]);
+      for (int i = 0; i < EG_MAX_VEC; ++i) {
+        const int v = threadIdx.x + i * EG_SUM_THREADS;
+        if (v < nvec) eg_add8(acc[i], src[v]);
       }
+    }
+    const bool whole_row = (L <= EG_CHUNK);
 #pragma unroll
-      for (int i = 0; i < EG_LANE_VECS; ++i) {
-        const int v = v0 + lane + 32 * i;
-        if (v >= nvec) continue;
-        if (whole_row) {
-          eg_update8(grad + static_cast<size_t>(row) * H + v * 8, acc[i], scale);
-        } else {
-          float4* dst = reinterpret_cast<float4*>(partial + static_cast<size_t>(pstart[u] + k) * H + v * 8);
-          dst[0] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-          dst[1] = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
-        }
+    for (int i = 0; i < EG_MAX_VEC; ++i) {
+      const int v = threadIdx.x + i * EG_SUM_THREADS;
+      if (v >= nvec) continue;
+      if (whole_row) {
+        eg_update8(grad + static_cast<size_t>(row) * H + v * 8, acc[i], scale);
+      } else {
+        float4* dst = reinterpret_cast<float4*>(partial + static_cast<size_t>(pstart[u] + k) * H + v * 8);
+        dst[0] = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        dst[1] = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
       }
     }
   }
@@ -358,8 +346,8 @@ int b200sft_embed_grad_rows(const uint64_t* ids_ptrs_host, const uint64_t* dy_pt
   if (!ids_ptrs_host || !dy_ptrs_host || !n_ptrs_host || !grad) return fail(B200SFT_ERR_INVALID, "null pointer");
   if (world <= 0 || world > EG_MAX_PEERS) return fail(B200SFT_ERR_INVALID, "world %d out of range (1..%d)", world, EG_MAX_PEERS);
   if (cap <= 0 || V <= 0 || H <= 0) return fail(B200SFT_ERR_INVALID, "cap, V, H must be positive (got %d, %d, %d)", cap, V, H);
-  if (H % 8 != 0 || H > EG_MAX_H)
-    return fail(B200SFT_ERR_INVALID, "H must be a multiple of 8 and at most %d (got %d)", EG_MAX_H, H);
+  if (H % 8 != 0 || H > EG_SUM_THREADS * EG_MAX_VEC * 8)
+    return fail(B200SFT_ERR_INVALID, "H must be a multiple of 8 and at most %d (got %d)", EG_SUM_THREADS * EG_MAX_VEC * 8, H);
   if (static_cast<long long>(world) * cap >= (1LL << 31)) return fail(B200SFT_ERR_INVALID, "world * cap must stay below 2^31");
   if ((reinterpret_cast<uintptr_t>(grad) & 15) != 0) return fail(B200SFT_ERR_INVALID, "grad must be 16-byte aligned");
   const size_t need = b200sft_embed_grad_workspace_bytes(world, cap, V, H);

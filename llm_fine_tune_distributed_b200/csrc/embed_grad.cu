@@ -86,11 +86,15 @@ __global__ void eg_prefix_blocks_kernel(int32_t* __restrict__ hist, int n_blocks
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= V) return;
   int run = 0;
-  for (int b = 0; b < n_blocks; ++b) {
-    int32_t* h = hist + static_cast<size_t>(b) * V + v;
-    const int c = *h;
-    *h = run;
-    run += c;
+  for (int b0 = 0; b0 < n_blocks; b0 += 8) {  // eight independent loads in flight, then the running sum
+    int c[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) c[i] = (b0 + i < n_blocks) ? hist[static_cast<size_t>(b0 + i) * V + v] : 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (b0 + i < n_blocks) hist[static_cast<size_t>(b0 + i) * V + v] = run;
+      run += c[i];
+    }
   }
   count[v] = run;
 }

@@ -128,10 +128,12 @@ struct FwdSoftmaxEpi {
 struct Bf16TileStore {
   uint8_t* smem;  // this warp's EPI_WARP_SMEM_BYTES
   int lane;
+  uint64_t policy;  // L2 eviction priority of the stored lines (L2_EVICT_* in sm100_ptx.cuh)
 
-  __device__ __forceinline__ void init(uint8_t* warp_smem) {
+  __device__ __forceinline__ void init(uint8_t* warp_smem, uint64_t l2_policy = L2_EVICT_NORMAL) {
     smem = warp_smem;
     lane = threadIdx.x & 31;
+    policy = l2_policy ? l2_policy : L2_EVICT_NORMAL;
   }
 
   // `half` = which 32-column half of the 64-column block these values fill.
@@ -159,7 +161,7 @@ struct Bf16TileStore {
     fence_proxy_async_smem();
     __syncwarp();
     if (lane == 0) {
-      tma_store_2d(map, smem, col0, row0);
+      tma_store_2d(map, smem, col0, row0, policy);
       tma_store_commit();
     }
   }
@@ -184,6 +186,7 @@ struct DlogitsEpi {
                           // Rows in [live rows, rows_alloc) are written as zeros because the dW GEMM
                           // contracts over them in whole 64-row blocks.
     int col_offset;       // first vocabulary column of the slab (labels are global column indices)
+    uint64_t store_policy;  // L2 eviction priority of the dlogits stores (0 = normal)
   };
   const Params& p;
   const int M, N;
@@ -195,7 +198,7 @@ struct DlogitsEpi {
     float c = __ldg(p.grad_out) * p.scale;
     if (p.denom != nullptr) c = c / static_cast<float>(__ldg(p.denom));
     coef_all = c;
-    st.init(warp_smem);
+    st.init(warp_smem, p.store_policy);
   }
   __device__ __forceinline__ void finish() { st.drain(); }
 
@@ -685,7 +688,7 @@ namespace {
 
 // Tuning switches, read from the environment at each call (measurement aid; the defaults are what ships):
 //   B200SFT_L2_HINTS=mask   bit 0: evict_last on the operand every tile re-reads; bit 1: evict_first on the operand
-//                           that is streamed once (0 = TMA loads without eviction-priority hints)
+//                           that is streamed once; bit 2: evict_first on the dlogits STORES (0 = no hints)
 //   B200SFT_DX_KS_MAJOR=0   dX work units tile-major (the round-1 order) instead of K-split-major
 //   B200SFT_DX_MIN_SPLITS=n force at least n K-splits of the dX GEMM (power of two); B200SFT_DX_MAX_SPLITS=n the cap (4)
 int tune_int(const char* name, int dflt) {
@@ -958,6 +961,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     rc = make_store_tmap(&dp.out_map, dlog, N, cols, slab);
     if (rc != 0) return rc;
     dp.col_offset = v0;
+    dp.store_policy = (tune_int("B200SFT_L2_HINTS", 1) & 4) ? L2_EVICT_FIRST : 0;
     rc = launch_gemm<DlogitsEpi, false, false>(x, H, ws_rows, H, N, cols, H, /*m_fastest=*/1, dp, stream,
                                                logit_gemm_opts(n_rows_dev));
     if (rc != 0) return rc;

@@ -26,6 +26,16 @@ def peaks():
     return 1590.0, 6650.0, "fallback"
 
 
+def sustained_peak():
+    """cuBLAS bf16 throughput under sustained load (the denominator for cases that run long enough to sit at the power
+    cap, i.e. every case of a 20-iteration sweep); falls back to the burst figure."""
+    p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", d["bf16_tflops"])
+    return 1400.0
+
+
 def time_ms(fn, iters, warmup, flush):
     for _ in range(warmup):
         fn()
@@ -167,6 +177,9 @@ def main():
                     "fused_fwd_frac_of_peak": round(fl_f / t_f / 1e9 / peak_tf, 4),
                     "fused_fwd_bwd_frac_of_peak": round(fl_fb / (t_f + t_b) / 1e9 / peak_tf, 4),
                     "peak_tflops": peak_tf, "peak_kind": peak_kind,
+                    "sustained_peak_tflops": sustained_peak(),
+                    "fused_fwd_frac_of_sustained_peak": round(fl_f / t_f / 1e9 / sustained_peak(), 4),
+                    "fused_fwd_bwd_frac_of_sustained_peak": round(fl_fb / (t_f + t_b) / 1e9 / sustained_peak(), 4),
                     "fused_peak_mem_gb": round(fused_mem / 2**30, 3),
                     "fused_loss": float(out["f"][0]),
                 })

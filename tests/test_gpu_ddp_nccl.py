@@ -92,3 +92,73 @@ def test_comm_hook_nccl_world2_matches_stock_ddp():
             assert ret[r][name + "_same_on_all_ranks"], f"{name}: ranks disagree"
         assert ret[r]["nvlink_p2p_path"] == "p2p"
     print("nvlink hook path:", ret[0]["nvlink_path"])
+
+
+def _kernel_worker(rank, world, port, ret):
+    """One bucket, one call: both NVLink reduce kernels against the fp32 sum of the ranks' inputs."""
+    import ctypes
+
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import torch.distributed._symmetric_memory as symm_mem
+
+    from llm_fine_tune_distributed_b200 import _cabi
+
+    lib = _cabi.load()
+    n = 8 * world * 40961                                   # ragged in units of the kernel's granularity
+    arena = symm_mem.empty(n, dtype=torch.bfloat16, device=dev)
+    hdl = symm_mem.rendezvous(arena, dist.group.WORLD)
+    inputs = [(torch.randn(n, generator=torch.Generator().manual_seed(50 + r)) * 3).to(torch.bfloat16) for r in range(world)]
+    acc = torch.zeros(n, dtype=torch.float32)
+    for t in inputs:
+        acc += t.float()
+    scale = float(torch.tensor(1.0) / torch.tensor(float(world)))
+    exact = (acc * scale)
+    want = exact.to(torch.bfloat16)
+    out = {"multicast": bool(hdl.multicast_ptr)}
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    for path in ("p2p", "multimem"):
+        if path == "multimem" and not hdl.multicast_ptr:
+            continue
+        arena.copy_(inputs[rank].to(dev))
+        hdl.barrier(channel=0)
+        if path == "p2p":
+            ptrs = (ctypes.c_uint64 * world)(*[int(p) for p in hdl.buffer_ptrs])
+            rc = lib.b200sft_allreduce_scale_bf16_p2p(ptrs, n, rank, world, scale, stream)
+        else:
+            rc = lib.b200sft_allreduce_scale_bf16_multimem(int(hdl.multicast_ptr), n, rank, world, scale, stream)
+        assert rc == 0, lib.b200sft_last_error().decode()
+        hdl.barrier(channel=0)
+        torch.cuda.synchronize()
+        got = arena.cpu()
+        out[path + "_bit_exact"] = bool(torch.equal(got, want))
+        # one bf16 rounding of the exact fp32 value, whatever order the switch adds in: within half an ulp + fp32 noise
+        ulp = torch.maximum(exact.abs(), torch.tensor(1e-30)) * 2.0 ** -8
+        out[path + "_within_one_rounding"] = bool(((got.float() - exact).abs() <= ulp).all())
+        gathered = [torch.zeros_like(arena) for _ in range(world)]
+        dist.all_gather(gathered, arena)
+        out[path + "_same_on_all_ranks"] = all(torch.equal(gathered[0], t) for t in gathered[1:])
+        hdl.barrier(channel=0)
+    ret[rank] = out
+    dist.destroy_process_group()
+
+
+def test_nvlink_reduce_kernels_single_call_world2():
+    """The reduce kernels themselves, one call on real peers: the peer-load kernel bit for bit against
+    bf16(fp32 sum x 1/world); the multimem kernel (in-switch reduction, when the fabric offers a multicast address)
+    within ONE bf16 rounding of the exact sum and identical on every rank -- tighter than the 2^-5 the three-iteration
+    DDP comparison above can state."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ret = mp.Manager().dict()
+    mp.spawn(_kernel_worker, args=(2, 29651, ret), nprocs=2, join=True)
+    for r in range(2):
+        o = ret[r]
+        assert o["p2p_bit_exact"] and o["p2p_same_on_all_ranks"]
+        print(f"rank {r}: multicast address available: {o['multicast']}; multimem bit-exact vs fp32 sum: {o.get('multimem_bit_exact')}")
+        if o["multicast"]:
+            assert o["multimem_within_one_rounding"] and o["multimem_same_on_all_ranks"]

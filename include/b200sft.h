@@ -261,6 +261,9 @@ int b200sft_cast_bf16_to_f32(const void* src, float* dst, size_t n, float scale,
  *             multimem.st: the reduction and the broadcast happen inside the switch);
  *   p2p:      `peer_ptrs_host` is a HOST array of `world` device pointers, the bucket's address on
  *             each rank (own rank included), for boxes without multicast support.
+ * Precision: p2p returns bf16(fp32 sum * scale) exactly; the in-switch reduction of the multimem path hands back a
+ * bf16 sum that is not rounded to nearest (measured on B200: up to 1.92 * 2^-8 relative off the exact sum, i.e. within
+ * one bf16 spacing) -- the same order as the bf16 ring sum of the reference's NCCL allreduce.
  * Each rank processes slice `rank` of `world` equal slices; n (elements) must be a multiple of
  * 8*world.  The kernels never wait on another rank: the caller must order them across ranks with a
  * symmetric-memory barrier before (all copies written) and after (all results written) the call.

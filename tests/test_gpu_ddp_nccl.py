@@ -136,9 +136,12 @@ def _kernel_worker(rank, world, port, ret):
         torch.cuda.synchronize()
         got = arena.cpu()
         out[path + "_bit_exact"] = bool(torch.equal(got, want))
-        # one bf16 rounding of the exact fp32 value, whatever order the switch adds in: within half an ulp + fp32 noise
+        # unit: 2^-8 |exact| = the largest error ONE round-to-nearest bf16 rounding can make (half a spacing at the bottom
+        # of a binade).  The peer-load kernel stays within it by construction; the NVSwitch's multimem.ld_reduce was
+        # measured at up to 1.92 units on B200, i.e. its bf16 result is not rounded to nearest -- bound: one full spacing.
         ulp = torch.maximum(exact.abs(), torch.tensor(1e-30)) * 2.0 ** -8
-        out[path + "_within_one_rounding"] = bool(((got.float() - exact).abs() <= ulp).all())
+        out[path + "_within_one_rounding"] = bool(((got.float() - exact).abs() <= 2.0 * ulp).all())
+        out[path + "_max_err_ulps"] = float(((got.float() - exact).abs() / ulp).max())
         gathered = [torch.zeros_like(arena) for _ in range(world)]
         dist.all_gather(gathered, arena)
         out[path + "_same_on_all_ranks"] = all(torch.equal(gathered[0], t) for t in gathered[1:])
@@ -150,8 +153,8 @@ def _kernel_worker(rank, world, port, ret):
 def test_nvlink_reduce_kernels_single_call_world2():
     """The reduce kernels themselves, one call on real peers: the peer-load kernel bit for bit against
     bf16(fp32 sum x 1/world); the multimem kernel (in-switch reduction, when the fabric offers a multicast address)
-    within ONE bf16 rounding of the exact sum and identical on every rank -- tighter than the 2^-5 the three-iteration
-    DDP comparison above can state."""
+    within ONE bf16 spacing (2^-7 relative) of the exact sum and identical on every rank -- four times tighter than the
+    2^-5 the three-iteration DDP comparison above can state."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     ret = mp.Manager().dict()
@@ -159,6 +162,7 @@ def test_nvlink_reduce_kernels_single_call_world2():
     for r in range(2):
         o = ret[r]
         assert o["p2p_bit_exact"] and o["p2p_same_on_all_ranks"]
-        print(f"rank {r}: multicast address available: {o['multicast']}; multimem bit-exact vs fp32 sum: {o.get('multimem_bit_exact')}")
+        print(f"rank {r}: multicast address available: {o['multicast']}; multimem bit-exact vs fp32 sum: {o.get('multimem_bit_exact')}, "
+              f"max error {o.get('multimem_max_err_ulps')} ulps, same on all ranks {o.get('multimem_same_on_all_ranks')}")
         if o["multicast"]:
             assert o["multimem_within_one_rounding"] and o["multimem_same_on_all_ranks"]

@@ -174,3 +174,33 @@ def test_split_tied_gradient_matches_stock_ddp_gloo(world, train_all):
         assert o["replicas_identical"], "ranks ended with different tied gradients"
         print(f"world {world} rank {r}: tied gradient max-rel-err vs stock DDP {o['tied_rel_err']:.3e}, cos {o['tied_cos']:.6f}")
         assert o["tied_cos"] >= 0.9999 and o["tied_rel_err"] <= 2.0 ** -6
+
+
+def test_row_form_properties_random_cases():
+    """Property check of the row-wise restatement on random small cases (hypothesis): rows nobody touched keep their
+    bits; every touched row is within one bf16 rounding of the exact float64 update; duplicates of one token anywhere
+    (several ranks, segments longer than one 64-token chunk) are all counted; negative ids are skipped."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None)
+    @given(st.integers(1, 4), st.integers(1, 150), st.integers(2, 40), st.integers(0, 2**31 - 1))
+    def check(world, n, V, seed):
+        rng = np.random.default_rng(seed)
+        H = 8
+        bf = lambda a: torch.from_numpy(a.astype(np.float32)).to(torch.bfloat16).to(torch.float32).numpy()
+        grad = bf(rng.normal(size=(V, H)) * 0.1)
+        ids = [rng.integers(-1, V, size=n) for _ in range(world)]
+        dys = [bf(rng.normal(size=(n, H)) * 0.05) for _ in range(world)]
+        got = oracle.embed_grad_rows_numpy(grad, ids, dys, 1.0 / world)
+        exact = grad.astype(np.float64).copy()
+        for r in range(world):
+            for t in range(n):
+                if ids[r][t] >= 0:
+                    exact[ids[r][t]] += dys[r][t].astype(np.float64) / world
+        touched = np.unique(np.concatenate([i[i >= 0] for i in ids])) if any((i >= 0).any() for i in ids) else np.array([], dtype=int)
+        untouched = np.setdiff1d(np.arange(V), touched)
+        assert np.array_equal(got[untouched], grad[untouched])
+        # one bf16 rounding (2^-8 relative) of a value whose fp32 summation error is far below that
+        assert np.all(np.abs(got - exact) <= 2.0 ** -8 * np.abs(exact) + 1e-6)
+
+    check()

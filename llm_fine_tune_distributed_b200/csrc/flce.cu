@@ -126,23 +126,25 @@ struct FwdSoftmaxEpi {
 // lane issues a TMA store for it.  The TMA unit clips the box at the tensor's edges, so ragged
 // last tiles need no special handling.
 struct Bf16TileStore {
-  uint8_t* smem;  // this warp's EPI_WARP_SMEM_BYTES
+  uint8_t* smem;  // this warp's EPI_WARP_SMEM_BYTES: two staging tiles
   int lane;
+  int cur;          // staging tile being filled (0 / 1)
   uint64_t policy;  // L2 eviction priority of the stored lines (L2_EVICT_* in sm100_ptx.cuh)
 
   __device__ __forceinline__ void init(uint8_t* warp_smem, uint64_t l2_policy = L2_EVICT_NORMAL) {
     smem = warp_smem;
     lane = threadIdx.x & 31;
+    cur = 0;
     policy = l2_policy ? l2_policy : L2_EVICT_NORMAL;
   }
 
   // `half` = which 32-column half of the 64-column block these values fill.
   __device__ __forceinline__ void stage(const float (&g)[32], int half) {
-    if (half == 0) {  // the block buffer is about to be overwritten: the previous store must have read it
-      if (lane == 0) tma_store_wait_read<0>();
+    if (half == 0) {  // this tile was last handed to the TMA unit two stores ago: only the latest store may still be reading
+      if (lane == 0) tma_store_wait_read<1>();
       __syncwarp();
     }
-    uint8_t* row = smem + lane * 128;
+    uint8_t* row = smem + cur * EPI_STAGE_TILE_BYTES + lane * 128;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       uint4 v;
@@ -161,9 +163,10 @@ struct Bf16TileStore {
     fence_proxy_async_smem();
     __syncwarp();
     if (lane == 0) {
-      tma_store_2d(map, smem, col0, row0, policy);
+      tma_store_2d(map, smem + cur * EPI_STAGE_TILE_BYTES, col0, row0, policy);
       tma_store_commit();
     }
+    cur ^= 1;
   }
 
   __device__ __forceinline__ void drain() {

@@ -33,8 +33,10 @@ constexpr int TMEM_COLS = NUM_ACC_STAGES * BLOCK_N;  // 512: the whole TMEM of t
 constexpr int NUM_EPI_WARPS = 4;
 constexpr int GEMM_THREADS = 32 * (2 + NUM_EPI_WARPS);
 constexpr int SMEM_BARRIER_BYTES = 256;
-// Per-epilogue-warp staging tile for TMA stores: 32 rows x 128 B (64 bf16 columns), 128B-swizzled.
-constexpr int EPI_WARP_SMEM_BYTES = 32 * 128;
+// Per-epilogue-warp staging for TMA stores: two tiles of 32 rows x 128 B (64 bf16 columns), 128B-swizzled, used
+// alternately so that the warp fills one while the TMA unit still reads the other.
+constexpr int EPI_STAGE_TILE_BYTES = 32 * 128;
+constexpr int EPI_WARP_SMEM_BYTES = 2 * EPI_STAGE_TILE_BYTES;
 constexpr int EPI_SMEM_BYTES = NUM_EPI_WARPS * EPI_WARP_SMEM_BYTES;
 constexpr int GEMM_SMEM_BYTES =
     NUM_STAGES * STAGE_BYTES + EPI_SMEM_BYTES + 1024 /*alignment slack*/ + SMEM_BARRIER_BYTES;

@@ -253,6 +253,8 @@ struct StoreEpi {
     size_t split_stride;  // elements between the per-split accumulators (0 when the GEMM is not split)
     int ld;
     int mode;
+    float* tail_acc;      // [slots][tile rows][256] fp32: accumulators of the K pieces of tail tiles (GemmShape::tail_split)
+    int tail_tile_rows;   // rows of one tile in that scratch (256 for the pair engine, 128 for the single-CTA one)
   };
   const Params& p;
   const int M, N;
@@ -267,6 +269,15 @@ struct StoreEpi {
 
   __device__ __forceinline__ void chunk(const TileCoord& tc, int row_in_tile, int c, const uint32_t (&acc)[32]) {
     const int col0 = tc.n0 + c;
+    if (tc.tail_slot >= 0) {  // a K piece of a tail tile: the raw accumulator goes to its scratch slot, whole tile
+      float4* dst = reinterpret_cast<float4*>(
+          p.tail_acc + (static_cast<size_t>(tc.tail_slot) * p.tail_tile_rows + tc.row_off + row_in_tile) * BLOCK_N + c);
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        dst[q] = make_float4(__uint_as_float(acc[q * 4 + 0]), __uint_as_float(acc[q * 4 + 1]),
+                             __uint_as_float(acc[q * 4 + 2]), __uint_as_float(acc[q * 4 + 3]));
+      return;
+    }
     if (col0 >= N) return;  // warp-uniform
     float v[32];
 #pragma unroll
@@ -486,6 +497,38 @@ __global__ void dx_combine_splits_kernel(const float* __restrict__ acc, size_t s
   }
 }
 
+// out[tile] = bf16( sum over the K pieces of a tail tile, in piece order ).  One block per tail tile; the tile's place
+// follows from the same UnitPlan the GEMM used (tile_n fastest).  Rows / columns beyond the output are clipped.
+__global__ void __launch_bounds__(256)
+    tail_combine_kernel(const float* __restrict__ tail_acc, UnitPlan plan, int tile_rows, int tiles_n, int M, int N, int ldc,
+                        __nv_bfloat16* __restrict__ out) {
+  const int t = blockIdx.x;  // tail tile index
+  const int tile = plan.full_tiles + t;
+  const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
+  const size_t tile_elems = static_cast<size_t>(tile_rows) * BLOCK_N;
+  for (int i = threadIdx.x; i < tile_rows * (BLOCK_N / 4); i += blockDim.x) {
+    const int r = i / (BLOCK_N / 4), c4 = (i - r * (BLOCK_N / 4)) * 4;
+    const int row = tile_m * tile_rows + r, col = tile_n * BLOCK_N + c4;
+    if (row >= M || col >= N) continue;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < plan.tail_splits; ++k) {
+      const float4 x = *reinterpret_cast<const float4*>(
+          tail_acc + (static_cast<size_t>(t) * plan.tail_splits + k) * tile_elems + static_cast<size_t>(r) * BLOCK_N + c4);
+      v.x += x.x;
+      v.y += x.y;
+      v.z += x.z;
+      v.w += x.w;
+    }
+    __nv_bfloat16* o = out + static_cast<size_t>(row) * ldc + col;
+    if (col + 4 <= N) {
+      *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    } else {
+      const float e[4] = {v.x, v.y, v.z, v.w};
+      for (int j = 0; j < 4 && col + j < N; ++j) o[j] = __float2bfloat16_rn(e[j]);
+    }
+  }
+}
+
 // =============================================================================================
 // Host side
 // =============================================================================================
@@ -580,6 +623,7 @@ struct GemmOpts {
   int max_k_splits = 1, min_k_splits = 1;
   int ks_major = 0;
   uint64_t a_l2_policy = 0, b_l2_policy = 0;
+  int tail_split = 0;  // StoreEpi launches only: the caller supplies Params::tail_acc and runs launch_tail_combine after
 };
 
 template <class Epi, bool A_MN, bool B_MN, int BN = 256>
@@ -610,6 +654,7 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.ks_major = o.ks_major;
   s.a_l2_policy = o.a_l2_policy;
   s.b_l2_policy = o.b_l2_policy;
+  s.tail_split = o.tail_split;
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
   if (!paired) {
     auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
@@ -820,6 +865,17 @@ int dx_min_k_splits(int N, int H, int slab_cols) {
   return forced > 0 ? (forced < maxs ? forced : maxs) : 1;
 }
 
+// dW GEMM of one slab: [cols, H] output, tile_n fastest.  Its last wave is usually a sliver (2008 tiles on 74 pairs),
+// so the tiles of that wave are K-split into one short wave (GemmShape::tail_split); B200SFT_DW_TAIL_SPLIT=0 turns it off.
+bool dw_tail_split_on() { return tune_int("B200SFT_DW_TAIL_SPLIT", 1) != 0; }
+UnitPlan dw_unit_plan(int cols, int H) {
+  const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
+  const int tiles = ((cols + tile_m - 1) / tile_m) * ((H + BLOCK_N - 1) / BLOCK_N);
+  return make_unit_plan(tiles, gemm_workers(cols, H), /*num_kb=*/0, 1, 1, 0, dw_tail_split_on() ? 1 : 0);
+}
+// One fp32 tile per worker at most (tail tiles x pieces <= workers): 148 x 128 x 256 x 4 B = 19.4 MB.
+size_t dw_tail_scratch_bytes() { return align_up(static_cast<size_t>(num_sms()) * BLOCK_M * BLOCK_N * sizeof(float), 1024); }
+
 }  // namespace
 
 // =============================================================================================
@@ -904,6 +960,7 @@ size_t b200sft_flce_bwd_workspace_bytes(int N, int H, int V, int chunk_cols) {
   const int splits = dx_max_k_splits(N, H);
   if (c < V || splits > 1)  // fp32 dX accumulator(s): across slabs and / or across K-splits
     b += static_cast<size_t>(splits) * align_up(static_cast<size_t>(N) * H * sizeof(float), 1024);
+  b += dw_tail_scratch_bytes();  // K pieces of the dW GEMM's tail tiles
   return b;
 }
 
@@ -912,7 +969,12 @@ int b200sft_flce_bwd_launch_count(int N, int H, int V, int chunk_cols, int need_
   const int slab = resolve_slab_cols(N, V, chunk_cols);
   const int num_slabs = (V + slab - 1) / slab;
   const int combine = (need_dx && dx_max_k_splits(N, H) > 1) ? 1 : 0;
-  return num_slabs * (1 + (need_dx ? 1 : 0) + (need_dw ? 1 : 0)) + combine;
+  int tails = 0;
+  for (int si = 0; need_dw && si < num_slabs; ++si) {
+    const int cols = (V - si * slab) < slab ? (V - si * slab) : slab;
+    tails += dw_unit_plan(cols, H).tail_splits > 1 ? 1 : 0;
+  }
+  return num_slabs * (1 + (need_dx ? 1 : 0) + (need_dw ? 1 : 0)) + combine + tails;
 }
 
 int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const float* lse, const float* grad_out,
@@ -943,6 +1005,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
   __nv_bfloat16* dlog = reinterpret_cast<__nv_bfloat16*>(ws);
   ws += align_up(static_cast<size_t>(N) * slab * sizeof(__nv_bfloat16), 1024);
   float* dx_acc = (num_slabs > 1 || dx_splits > 1) ? reinterpret_cast<float*>(ws) : nullptr;
+  if (dx_acc != nullptr) ws += static_cast<size_t>(dx_splits) * align_up(static_cast<size_t>(N) * H * sizeof(float), 1024);
+  float* dw_tail_acc = reinterpret_cast<float*>(ws);
 
   const __nv_bfloat16* wb = static_cast<const __nv_bfloat16*>(w);
   __nv_bfloat16* dwb = static_cast<__nv_bfloat16*>(dw);
@@ -974,6 +1038,8 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     StoreEpi::Params sx;
     rc = make_store_tmap(&sx.out_map, dx, N, H, H);
     if (rc != 0) return rc;
+    sx.tail_acc = nullptr;
+    sx.tail_tile_rows = 0;
     sx.acc = dx_acc;
     sx.split_stride = dx_splits > 1 ? dx_split_stride : 0;
     sx.ld = H;
@@ -1008,13 +1074,22 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     sw.split_stride = 0;
     sw.ld = H;
     sw.mode = STORE_BF16;
+    sw.tail_acc = dw_tail_acc;
+    sw.tail_tile_rows = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
     GemmOpts ow;  // every wave of vocabulary tiles contracts over all of X: keep X, let dlogits stream past it
     ow.dyn_rows = n_rows_dev;
     ow.dyn_is_k = 1;
     ow.a_l2_policy = stream_policy();
     ow.b_l2_policy = keep_policy();
+    ow.tail_split = dw_tail_split_on() ? 1 : 0;
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, ow);
     if (rc != 0) return rc;
+    const UnitPlan wp = dw_unit_plan(cols, H);
+    if (wp.tail_splits > 1) {  // add up the K pieces of the last wave's tiles
+      tail_combine_kernel<<<wp.num_tiles - wp.full_tiles, 256, 0, stream>>>(
+          dw_tail_acc, wp, sw.tail_tile_rows, (H + BLOCK_N - 1) / BLOCK_N, cols, H, H, dwb + static_cast<size_t>(v0) * H);
+      B200_CUDA_CHECK(cudaGetLastError());
+    }
   }
   if (dx_splits > 1 && dx != nullptr) {
     const int tile_m = (g_cta_group == 2) ? pair::TILE_M : BLOCK_M;
@@ -1047,6 +1122,8 @@ int b200sft_gemm_bf16(const void* a, const void* b, void* c, int M, int N, int K
   sp.split_stride = 0;
   sp.ld = ldc;
   sp.mode = STORE_BF16;
+  sp.tail_acc = nullptr;
+  sp.tail_tile_rows = 0;
   if (!a_mn_major && !b_mn_major) return launch_gemm<StoreEpi, false, false>(a, lda, b, ldb, M, N, K, 0, sp, stream);
   if (!a_mn_major && b_mn_major) return launch_gemm<StoreEpi, false, true>(a, lda, b, ldb, M, N, K, 0, sp, stream);
   if (a_mn_major && !b_mn_major) return launch_gemm<StoreEpi, true, false>(a, lda, b, ldb, M, N, K, 0, sp, stream);

@@ -65,11 +65,18 @@ struct GemmShape {
   int ks_major;
   // L2 eviction priority of the TMA loads of each operand (L2_EVICT_* in sm100_ptx.cuh; 0 = normal).
   uint64_t a_l2_policy, b_l2_policy;
+  // Tail splitting (unsplit, tile_n-fastest GEMMs with a static tile count, i.e. dW): when the last wave of tiles
+  // would leave most workers idle (2008 tiles on 74 CTA pairs: a 28th wave that is 13 % full), each of those last
+  // tiles is cut into workers / tail K pieces that run as one short wave; every piece leaves its fp32 accumulator in
+  // a scratch slot (TileCoord::tail_slot) and a small kernel adds the slots in fixed order.  See make_unit_plan.
+  int tail_split;
 };
 
 struct TileCoord {
   int m0, n0, tile_m, tile_n;
-  int ks;  // K-split index of this work unit (0 when the GEMM is not split)
+  int ks;         // K-split index of this work unit (0 when the GEMM is not split)
+  int tail_slot;  // >= 0: this unit is a K piece of a tail tile; its accumulator goes to that scratch slot
+  int row_off;    // first row of this CTA inside the tile (cta_group::2: 0 or 128)
 };
 
 // Smallest power of two in [min_splits, max_splits] for which `tiles * splits` work units fill `workers` to
@@ -86,22 +93,63 @@ __host__ __device__ inline int choose_k_splits(int tiles, int workers, int max_s
   return s;
 }
 
+// The work-unit schedule of one launch.  A pure function of its arguments: the kernels, the host (scratch sizing, the
+// launch of the tail-combine kernel) and the combine kernels all derive it from the same values.
+constexpr int MAX_TAIL_SPLITS = 16;
+struct UnitPlan {
+  int num_tiles, num_kb, splits, ks_major;
+  int full_tiles;   // tiles that run as whole units (== num_tiles when the tail is not split)
+  int tail_splits;  // K pieces per tail tile (1 = no tail splitting)
+  int num_units;
+};
+__host__ __device__ inline UnitPlan make_unit_plan(int num_tiles, int workers, int num_kb, int max_k_splits,
+                                                   int min_k_splits, int ks_major, int tail_split) {
+  UnitPlan p;
+  p.num_tiles = num_tiles;
+  p.num_kb = num_kb;
+  p.splits = choose_k_splits(num_tiles, workers, max_k_splits > 0 ? max_k_splits : 1, min_k_splits);
+  p.ks_major = ks_major;
+  p.full_tiles = num_tiles;
+  p.tail_splits = 1;
+  const int tail = workers > 0 ? num_tiles % workers : 0;
+  if (tail_split && p.splits == 1 && tail > 0 && num_tiles > workers && workers / tail >= 2) {
+    p.tail_splits = workers / tail < MAX_TAIL_SPLITS ? workers / tail : MAX_TAIL_SPLITS;
+    p.full_tiles = num_tiles - tail;
+  }
+  p.num_units = p.tail_splits > 1 ? p.full_tiles + tail * p.tail_splits : num_tiles * p.splits;
+  return p;
+}
+
 // Work unit -> (tile, k-split) and the unit's k-block range [kb0, kb1).
 struct UnitRange {
-  int tile, ks, kb0, kb1;
+  int tile, ks, kb0, kb1, tail_slot;
 };
-__device__ __forceinline__ UnitRange unit_range(int unit, int splits, int num_kb, int num_tiles, int ks_major) {
+__device__ __forceinline__ UnitRange unit_range(const UnitPlan& p, int unit) {
   UnitRange u;
-  if (ks_major) {
-    u.ks = unit / num_tiles;
-    u.tile = unit - u.ks * num_tiles;
+  int pieces = p.splits;
+  u.tail_slot = -1;
+  if (p.tail_splits > 1) {
+    if (unit < p.full_tiles) {
+      u.tile = unit;
+      u.ks = 0;
+      pieces = 1;
+    } else {
+      u.tail_slot = unit - p.full_tiles;
+      u.tile = p.full_tiles + u.tail_slot / p.tail_splits;
+      u.ks = u.tail_slot - (u.tile - p.full_tiles) * p.tail_splits;
+      pieces = p.tail_splits;
+    }
+  } else if (p.ks_major) {
+    u.ks = unit / p.num_tiles;
+    u.tile = unit - u.ks * p.num_tiles;
   } else {
-    u.tile = unit / splits;
-    u.ks = unit - u.tile * splits;
+    u.tile = unit / p.splits;
+    u.ks = unit - u.tile * p.splits;
   }
-  const int per = (num_kb + splits - 1) / splits;
+  const int per = (p.num_kb + pieces - 1) / pieces;
   u.kb0 = u.ks * per;
-  u.kb1 = u.kb0 + per < num_kb ? u.kb0 + per : num_kb;
+  u.kb1 = u.kb0 + per < p.num_kb ? u.kb0 + per : p.num_kb;
+  if (u.kb0 > p.num_kb) u.kb0 = p.num_kb;
   if (u.kb1 < u.kb0) u.kb1 = u.kb0;
   return u;
 }
@@ -123,6 +171,8 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile) {
   c.m0 = c.tile_m * BLOCK_M;
   c.n0 = c.tile_n * BLOCK_N;
   c.ks = 0;
+  c.tail_slot = -1;
+  c.row_off = 0;
   return c;
 }
 
@@ -168,8 +218,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
-  const int splits = choose_k_splits(num_tiles, gridDim.x, shape.max_k_splits > 0 ? shape.max_k_splits : 1, shape.min_k_splits);
-  const int num_units = num_tiles * splits;
+  const UnitPlan plan = make_unit_plan(num_tiles, gridDim.x, num_kb, shape.max_k_splits, shape.min_k_splits, shape.ks_major,
+                                       shape.tail_split && !shape.m_fastest && (shape.dyn_rows == nullptr || shape.dyn_is_k));
+  const int num_units = plan.num_units;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -198,7 +249,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+        const UnitRange ur = unit_range(plan, unit);
         const TileCoord tc = tile_coord(shape, ur.tile);
         for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -241,7 +292,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       uint32_t phase = 0;
       int it = 0;
       for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
-        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+        const UnitRange ur = unit_range(plan, unit);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
@@ -275,9 +326,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
-      const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+      const UnitRange ur = unit_range(plan, unit);
       TileCoord tc = tile_coord(shape, ur.tile);
       tc.ks = ur.ks;
+      tc.tail_slot = ur.tail_slot;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       epi.tile_begin(tc, row_in_tile);
@@ -361,6 +413,8 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmShape& s, int tile, in
   c.m0 = c.tile_m * TILE_M + cta_rank * BLOCK_M;
   c.n0 = c.tile_n * BN;
   c.ks = 0;
+  c.tail_slot = -1;
+  c.row_off = cta_rank * BLOCK_M;
   return c;
 }
 
@@ -404,8 +458,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
   const int num_pairs = gridDim.x >> 1;
   const int num_tiles = shape.tiles_m * shape.tiles_n;
   const int num_kb = (shape.K + BLOCK_K - 1) / BLOCK_K;
-  const int splits = choose_k_splits(num_tiles, num_pairs, shape.max_k_splits > 0 ? shape.max_k_splits : 1, shape.min_k_splits);
-  const int num_units = num_tiles * splits;
+  const UnitPlan plan = make_unit_plan(num_tiles, num_pairs, num_kb, shape.max_k_splits, shape.min_k_splits, shape.ks_major,
+                                       shape.tail_split && !shape.m_fastest && (shape.dyn_rows == nullptr || shape.dyn_is_k));
+  const int num_units = plan.num_units;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -434,7 +489,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int unit = pair_id; unit < num_units; unit += num_pairs) {
-        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+        const UnitRange ur = unit_range(plan, unit);
         const TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
         const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
         for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
@@ -475,7 +530,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       uint32_t phase = 0;
       int it = 0;
       for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
-        const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+        const UnitRange ur = unit_range(plan, unit);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&acc_empty_bar[as], aphase ^ 1);
@@ -509,9 +564,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     Epi epi(epi_params, shape, smem_epi + (warp - 2) * EPI_WARP_SMEM_BYTES);
     int it = 0;
     for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
-      const UnitRange ur = unit_range(unit, splits, num_kb, num_tiles, shape.ks_major);
+      const UnitRange ur = unit_range(plan, unit);
       TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
       tc.ks = ur.ks;
+      tc.tail_slot = ur.tail_slot;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       epi.tile_begin(tc, row_in_tile);

@@ -46,10 +46,12 @@ def test_version_and_workspace_queries(lib):
     one = lib.b200sft_flce_bwd_workspace_bytes(4096, 2048, 128256, 0)       # 1 GiB budget: single slab
     two = lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 0)       # two slabs of 64256 columns
     big = lib.b200sft_flce_bwd_workspace_bytes(65536, 2048, 128256, 0)      # 16 slabs of 8192, dX not split
-    assert one == 4096 * 128256 * 2 + 4 * 4096 * 2048 * 4
-    assert two == 8192 * 64256 * 2 + 4 * 8192 * 2048 * 4
-    assert big == 65536 * 8192 * 2 + 65536 * 2048 * 4
-    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 128256) == 8192 * 128256 * 2 + 4 * 8192 * 2048 * 4
+    # ... + one fp32 128x256 tile per SM for the K pieces of the dW GEMM's tail tiles (148 SMs assumed without a GPU)
+    tail = 148 * 128 * 256 * 4
+    assert one == 4096 * 128256 * 2 + 4 * 4096 * 2048 * 4 + tail
+    assert two == 8192 * 64256 * 2 + 4 * 8192 * 2048 * 4 + tail
+    assert big == 65536 * 8192 * 2 + 65536 * 2048 * 4 + tail
+    assert lib.b200sft_flce_bwd_workspace_bytes(8192, 2048, 128256, 128256) == 8192 * 128256 * 2 + 4 * 8192 * 2048 * 4 + tail
 
 
 def test_argument_validation_without_launching(lib):

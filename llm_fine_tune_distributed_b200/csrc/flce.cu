@@ -497,8 +497,10 @@ __global__ void dx_combine_splits_kernel(const float* __restrict__ acc, size_t s
   }
 }
 
-// out[tile] = bf16( sum over the K pieces of a tail tile, in piece order ).  One block per tail tile; the tile's place
-// follows from the same UnitPlan the GEMM used (tile_n fastest).  Rows / columns beyond the output are clipped.
+// out[tile] = bf16( sum over the K pieces of a tail tile, in piece order ).  grid = (tail tiles, row groups of
+// TAIL_COMBINE_ROWS); the tile's place follows from the same UnitPlan the GEMM used (tile_n fastest).  Rows / columns
+// beyond the output are clipped.
+constexpr int TAIL_COMBINE_ROWS = 8;
 __global__ void __launch_bounds__(256)
     tail_combine_kernel(const float* __restrict__ tail_acc, UnitPlan plan, int tile_rows, int tiles_n, int M, int N, int ldc,
                         __nv_bfloat16* __restrict__ out) {
@@ -506,8 +508,9 @@ __global__ void __launch_bounds__(256)
   const int tile = plan.full_tiles + t;
   const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
   const size_t tile_elems = static_cast<size_t>(tile_rows) * BLOCK_N;
-  for (int i = threadIdx.x; i < tile_rows * (BLOCK_N / 4); i += blockDim.x) {
-    const int r = i / (BLOCK_N / 4), c4 = (i - r * (BLOCK_N / 4)) * 4;
+  for (int i = threadIdx.x; i < TAIL_COMBINE_ROWS * (BLOCK_N / 4); i += blockDim.x) {
+    const int r = blockIdx.y * TAIL_COMBINE_ROWS + i / (BLOCK_N / 4), c4 = (i % (BLOCK_N / 4)) * 4;
+    if (r >= tile_rows) continue;
     const int row = tile_m * tile_rows + r, col = tile_n * BLOCK_N + c4;
     if (row >= M || col >= N) continue;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1086,7 +1089,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     if (rc != 0) return rc;
     const UnitPlan wp = dw_unit_plan(cols, H);
     if (wp.tail_splits > 1) {  // add up the K pieces of the last wave's tiles
-      tail_combine_kernel<<<wp.num_tiles - wp.full_tiles, 256, 0, stream>>>(
+      tail_combine_kernel<<<dim3(wp.num_tiles - wp.full_tiles, sw.tail_tile_rows / TAIL_COMBINE_ROWS), 256, 0, stream>>>(
           dw_tail_acc, wp, sw.tail_tile_rows, (H + BLOCK_N - 1) / BLOCK_N, cols, H, H, dwb + static_cast<size_t>(v0) * H);
       B200_CUDA_CHECK(cudaGetLastError());
     }

@@ -626,6 +626,7 @@ struct GemmOpts {
   int max_k_splits = 1, min_k_splits = 1;
   int ks_major = 0;
   uint64_t a_l2_policy = 0, b_l2_policy = 0;
+  int k_pingpong = 0;
   int tail_split = 0;  // StoreEpi launches only: the caller supplies Params::tail_acc and runs launch_tail_combine after
 };
 
@@ -658,6 +659,7 @@ int launch_gemm(const void* a, int lda, const void* b, int ldb, int M, int N, in
   s.a_l2_policy = o.a_l2_policy;
   s.b_l2_policy = o.b_l2_policy;
   s.tail_split = o.tail_split;
+  s.k_pingpong = o.k_pingpong;
   const long long tiles = static_cast<long long>(s.tiles_m) * s.tiles_n;
   if (!paired) {
     auto kern = gemm_tcgen05_kernel<Epi, A_MN, B_MN>;
@@ -741,6 +743,7 @@ namespace {
 //   B200SFT_L2_HINTS=mask   bit 0: evict_last on the operand every tile re-reads; bit 1: evict_first on the operand
 //                           that is streamed once; bit 2: evict_first on the dlogits STORES (0 = no hints)
 //   B200SFT_DX_KS_MAJOR=0   dX work units tile-major (the round-1 order) instead of K-split-major
+//   B200SFT_K_PINGPONG=mask bit 0: dX, bit 1: dW -- alternate the K sweep direction from unit to unit (GemmShape)
 //   B200SFT_DX_MIN_SPLITS=n force at least n K-splits of the dX GEMM (power of two); B200SFT_DX_MAX_SPLITS=n the cap (4)
 int tune_int(const char* name, int dflt) {
   const char* v = getenv(name);
@@ -1061,6 +1064,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     ox.max_k_splits = dx_splits;
     ox.min_k_splits = dx_min_splits;
     ox.ks_major = tune_int("B200SFT_DX_KS_MAJOR", 1);
+    ox.k_pingpong = tune_int("B200SFT_K_PINGPONG", 3) & 1;
     ox.a_l2_policy = stream_policy();
     ox.b_l2_policy = keep_policy();
     rc = launch_gemm<StoreEpi, false, true, DX_TILE_N>(dlog, slab, ws_rows, H, N, H, cols, /*m_fastest=*/0, sx, stream, ox);
@@ -1085,6 +1089,7 @@ int b200sft_flce_bwd(const void* x, const void* w, const int32_t* labels, const 
     ow.a_l2_policy = stream_policy();
     ow.b_l2_policy = keep_policy();
     ow.tail_split = dw_tail_split_on() ? 1 : 0;
+    ow.k_pingpong = (tune_int("B200SFT_K_PINGPONG", 3) >> 1) & 1;
     rc = launch_gemm<StoreEpi, true, true>(dlog, slab, x, H, cols, H, N, /*m_fastest=*/0, sw, stream, ow);
     if (rc != 0) return rc;
     const UnitPlan wp = dw_unit_plan(cols, H);

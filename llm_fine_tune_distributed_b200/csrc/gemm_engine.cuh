@@ -70,6 +70,10 @@ struct GemmShape {
   // tiles is cut into workers / tail K pieces that run as one short wave; every piece leaves its fp32 accumulator in
   // a scratch slot (TileCoord::tail_slot) and a small kernel adds the slots in fixed order.  See make_unit_plan.
   int tail_split;
+  // Alternate the direction of the K sweep from one work unit of a worker to its next (all workers of a wave hold the
+  // same parity): the K range the previous wave touched last is the one the next wave touches first, so whatever part
+  // of the shared operand the L2 still holds is re-used instead of being evicted just before it is needed again.
+  int k_pingpong;
 };
 
 struct TileCoord {
@@ -248,10 +252,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       const uint64_t pol_b = shape.b_l2_policy ? shape.b_l2_policy : L2_EVICT_NORMAL;
       int stage = 0;
       uint32_t phase = 0;
-      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      int it = 0;
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, ++it) {
         const UnitRange ur = unit_range(plan, unit);
         const TileCoord tc = tile_coord(shape, ur.tile);
-        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
+        const bool rev = shape.k_pingpong && (it & 1);
+        for (int ki = ur.kb0; ki < ur.kb1; ++ki) {
+          const int kb = rev ? ur.kb0 + ur.kb1 - 1 - ki : ki;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -488,11 +495,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
       const uint64_t pol_b = shape.b_l2_policy ? shape.b_l2_policy : L2_EVICT_NORMAL;
       int stage = 0;
       uint32_t phase = 0;
-      for (int unit = pair_id; unit < num_units; unit += num_pairs) {
+      int it = 0;
+      for (int unit = pair_id; unit < num_units; unit += num_pairs, ++it) {
         const UnitRange ur = unit_range(plan, unit);
         const TileCoord tc = tile_coord<BN>(shape, ur.tile, cta_rank);
         const int b_row0 = tc.n0 + cta_rank * B_ROWS_PER_CTA;
-        for (int kb = ur.kb0; kb < ur.kb1; ++kb) {
+        const bool rev = shape.k_pingpong && (it & 1);
+        for (int ki = ur.kb0; ki < ur.kb1; ++ki) {
+          const int kb = rev ? ur.kb0 + ur.kb1 - 1 - ki : ki;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * CTA_STAGE_BYTES);  // both CTAs' bytes
           uint8_t* sa = smem_a + stage * A_BYTES;

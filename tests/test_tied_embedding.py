@@ -156,7 +156,7 @@ def _worker(rank, world, port, ret, train_all):
 
 
 @pytest.mark.timeout(600)
-@pytest.mark.parametrize("world,train_all", [(2, False), (3, False), (2, True)])
+@pytest.mark.parametrize("world,train_all", [(3, False), (2, True)])   # freeze policy at world 3; all layers trainable at world 2
 def test_split_tied_gradient_matches_stock_ddp_gloo(world, train_all):
     """train_all=True: every layer trains, so DDP's last bucket becomes ready AFTER the embedding-output hook ran --
     the case the re-queued end-of-backward callback exists for."""
